@@ -1,0 +1,200 @@
+"""Rank / device / topology layer.
+
+The reference's ``Communicator`` (``ddlb/communicator.py:1-80``) only parses the
+launcher environment and calls ``torch.cuda.set_device``; every implementation
+then creates and destroys its own process group. Here the communicator owns the
+whole life cycle:
+
+* rank / device selection (CUDA when present, otherwise a CPU mode so the
+  harness, the ``gloo`` baseline and the tests run without a GPU);
+* ONE ``torch.distributed`` process group per benchmark child, used only for
+  plumbing (handle exchange, max-over-ranks of timings, baselines);
+* the native symmetric heap (peer-mapped buffers + signal pads, see
+  ``ddlb_b200/parallel/symm_heap.py``) and the device-side barrier that the
+  fused kernels and the timing loop use;
+* an NVLink / NVSwitch topology report (``ddlb_b200/parallel/topology.py``).
+"""
+from __future__ import annotations
+
+import os
+from typing import Any, Dict, List, Optional
+
+from . import envs
+
+
+class Communicator:
+    """Process-wide singleton describing this rank and its peers."""
+
+    _instance: Optional["Communicator"] = None
+
+    def __new__(cls, *args, **kwargs):
+        if cls._instance is None:
+            cls._instance = super().__new__(cls)
+            cls._instance._initialized = False
+        return cls._instance
+
+    def __init__(self, device: Optional[str] = None):
+        if self._initialized:
+            return
+        import torch
+
+        self.rank = envs.get_rank()
+        self.local_rank = envs.get_local_rank()
+        self.world_size = envs.get_world_size()
+        self.local_size = envs.get_local_size()
+
+        kind = (device or envs.get_device_kind()).lower()
+        if kind == "auto":
+            kind = "cuda" if torch.cuda.is_available() else "cpu"
+        if kind == "cuda":
+            if not torch.cuda.is_available():
+                raise RuntimeError("DDLB_DEVICE=cuda requested but no CUDA device is visible")
+            ndev = torch.cuda.device_count()
+            if self.local_size > ndev:
+                raise RuntimeError(
+                    f"Local size {self.local_size} exceeds available CUDA devices {ndev}")
+            torch.cuda.set_device(self.local_rank)
+            self.device = torch.device(f"cuda:{self.local_rank}")
+        elif kind == "cpu":
+            self.device = torch.device("cpu")
+        else:
+            raise ValueError(f"Unknown device kind {kind!r} (expected cuda, cpu or auto)")
+
+        self._pg_owned = False
+        self._symm = None
+        self._sequence = int(os.environ.get("DDLB_CHILD_SEQUENCE", "0"))
+        self._initialized = True
+
+    # ------------------------------------------------------------------ basics
+    @property
+    def is_cuda(self) -> bool:
+        return self.device.type == "cuda"
+
+    @property
+    def default_backend(self) -> str:
+        return "nccl" if self.is_cuda else "gloo"
+
+    def __repr__(self) -> str:
+        return (f"Communicator(rank={self.rank}, world_size={self.world_size}, "
+                f"local_rank={self.local_rank}, local_size={self.local_size}, "
+                f"device={self.device})")
+
+    # ----------------------------------------------------------- process group
+    def init_process_group(self, backend: Optional[str] = None) -> None:
+        """Create the process group if none exists yet (idempotent).
+
+        Rendezvous is ``tcp://DDLB_MASTER_ADDR:port`` where the port rotates
+        with the child sequence number (see ``envs.rendezvous_port``). When
+        the default group already exists (e.g. ``bench.py`` under torchrun
+        initialised it from ``env://``) it is reused.
+        """
+        import torch.distributed as dist
+
+        if dist.is_initialized():
+            return
+        backend = backend or self.default_backend
+        if backend == "nccl" and not self.is_cuda:
+            raise RuntimeError("backend=nccl needs a CUDA device; use backend=gloo on CPU")
+        if backend.startswith("ucc"):
+            if not getattr(dist, "is_ucc_available", lambda: False)():
+                raise RuntimeError(
+                    "UCC is not available in this torch build "
+                    "(torch.distributed.is_ucc_available() is False)")
+            backend = "ucc"
+        addr = envs.get_master_addr()
+        port = envs.rendezvous_port(self._sequence)
+        kwargs: Dict[str, Any] = {}
+        if backend == "nccl":
+            kwargs["device_id"] = self.device
+        dist.init_process_group(backend=backend, rank=self.rank,
+                                world_size=self.world_size,
+                                init_method=f"tcp://{addr}:{port}", **kwargs)
+        self._pg_owned = True
+
+    @property
+    def pg_initialized(self) -> bool:
+        import torch.distributed as dist
+        return dist.is_available() and dist.is_initialized()
+
+    def barrier(self) -> None:
+        """Host-visible barrier: drain this device, then meet the other ranks."""
+        import torch
+        import torch.distributed as dist
+
+        if self.is_cuda:
+            torch.cuda.synchronize()
+        if self.world_size > 1 and dist.is_available() and dist.is_initialized():
+            if self._symm is not None:
+                # device barrier on the signal pads + host wait: no NCCL launch
+                self._symm.barrier()
+                torch.cuda.synchronize()
+            else:
+                dist.barrier()
+
+    def all_reduce_max(self, values: List[float]) -> List[float]:
+        """Element-wise max over ranks (reference ``ddlb/benchmark.py:191-204``)."""
+        import torch
+        import torch.distributed as dist
+
+        if self.world_size == 1:
+            return list(values)
+        self.init_process_group()
+        t = torch.tensor(values, dtype=torch.float64, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.tolist()
+
+    def all_gather_bytes(self, payload: bytes) -> List[bytes]:
+        """Gather one fixed-size byte string from every rank (handle exchange)."""
+        import torch
+        import torch.distributed as dist
+
+        if self.world_size == 1:
+            return [payload]
+        self.init_process_group()
+        mine = torch.frombuffer(bytearray(payload), dtype=torch.uint8).to(self.device)
+        out = torch.empty(self.world_size * mine.numel(), dtype=torch.uint8, device=self.device)
+        dist.all_gather_into_tensor(out, mine)
+        raw = out.cpu().numpy().tobytes()
+        n = len(payload)
+        return [raw[i * n:(i + 1) * n] for i in range(self.world_size)]
+
+    # ---------------------------------------------------------- symmetric heap
+    def symmetric_heap(self, min_bytes: int = 0):
+        """The rank's symmetric heap (created on first use, grown never)."""
+        if not self.is_cuda:
+            raise RuntimeError("the symmetric heap needs CUDA devices")
+        if self._symm is None:
+            from .parallel.symm_heap import SymmetricHeap
+            self._symm = SymmetricHeap(self, min_bytes)
+        elif min_bytes > self._symm.capacity:
+            raise RuntimeError(
+                f"symmetric heap already created with {self._symm.capacity} B; "
+                f"{min_bytes} B requested (set DDLB_SYMM_HEAP_BYTES)")
+        return self._symm
+
+    def topology(self) -> Dict[str, Any]:
+        from .parallel.topology import topology_report
+        return topology_report(self)
+
+    # ---------------------------------------------------------------- teardown
+    def shutdown(self) -> None:
+        import torch.distributed as dist
+
+        if self._symm is not None:
+            try:
+                self._symm.close()
+            finally:
+                self._symm = None
+        if self._pg_owned and dist.is_available() and dist.is_initialized():
+            try:
+                dist.destroy_process_group()
+            except Exception:
+                pass
+            self._pg_owned = False
+
+    @classmethod
+    def reset(cls) -> None:
+        """Drop the singleton (tests)."""
+        if cls._instance is not None and getattr(cls._instance, "_initialized", False):
+            cls._instance.shutdown()
+        cls._instance = None
