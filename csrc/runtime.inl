@@ -1,0 +1,199 @@
+// Symmetric heap (cudaIpc), device barrier, topology report. Included by ddlb_b200.cu.
+
+namespace ddlb {
+
+constexpr int64_t kSignalBytes = 1 << 20;   // zeroed signal pads at the start of every arena
+constexpr int kBarrierSlot = 0;             // words [0, 8) of the pads: barrier arrivals per source
+
+__global__ void barrier_kernel(uint32_t* sig_local, uint32_t* const* sig_peer_tbl_unused,
+                               uint32_t* p0, uint32_t* p1, uint32_t* p2, uint32_t* p3, uint32_t* p4,
+                               uint32_t* p5, uint32_t* p6, uint32_t* p7, int rank, int world,
+                               uint32_t epoch) {
+  uint32_t* peers[8] = {p0, p1, p2, p3, p4, p5, p6, p7};
+  const int t = threadIdx.x;
+  if (t < world && t != rank) {
+    // everything this stream did before the barrier is visible before the arrival
+    fence_acq_rel_sys();
+    st_release_sys(peers[t] + kBarrierSlot + rank, epoch);
+    wait_flag_ge<true>(sig_local + kBarrierSlot + t, epoch);
+  }
+}
+
+}  // namespace ddlb
+
+struct ddlb_symm {
+  int device = 0, rank = 0, world = 1;
+  int64_t bytes = 0;
+  void* base[DDLB_MAX_WORLD] = {};
+  bool opened[DDLB_MAX_WORLD] = {};
+  uint32_t barrier_epoch = 0;
+};
+
+extern "C" int ddlb_symm_create(int device, int rank, int world, int64_t bytes, ddlb_symm** out) {
+  using namespace ddlb;
+  if (out == nullptr) return set_error("null argument");
+  *out = nullptr;
+  if (world < 1 || world > DDLB_MAX_WORLD || rank < 0 || rank >= world)
+    return set_error("bad rank/world %d/%d", rank, world);
+  if (bytes < kSignalBytes * 2) bytes = kSignalBytes * 2;
+  bytes = (bytes + (2 << 20) - 1) / (2 << 20) * (2 << 20);
+  DDLB_CUDA(cudaSetDevice(device));
+  auto* s = new ddlb_symm();
+  s->device = device; s->rank = rank; s->world = world; s->bytes = bytes;
+  cudaError_t e = cudaMalloc(&s->base[rank], static_cast<size_t>(bytes));
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    delete s;
+    return set_error("cudaMalloc(%lld) for the symmetric heap: %s", (long long)bytes, cudaGetErrorString(e));
+  }
+  e = cudaMemset(s->base[rank], 0, static_cast<size_t>(kSignalBytes));
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    cudaFree(s->base[rank]);
+    delete s;
+    return set_error("clearing signal pads: %s", cudaGetErrorString(e));
+  }
+  *out = s;
+  return 0;
+}
+
+extern "C" int ddlb_symm_export(ddlb_symm* s, void* handle_out) {
+  using namespace ddlb;
+  if (s == nullptr || handle_out == nullptr) return set_error("null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == DDLB_IPC_HANDLE_BYTES, "handle size");
+  cudaIpcMemHandle_t h;
+  DDLB_CUDA(cudaSetDevice(s->device));
+  DDLB_CUDA(cudaIpcGetMemHandle(&h, s->base[s->rank]));
+  memcpy(handle_out, &h, sizeof(h));
+  return 0;
+}
+
+extern "C" int ddlb_symm_open_peers(ddlb_symm* s, const void* handles) {
+  using namespace ddlb;
+  if (s == nullptr || handles == nullptr) return set_error("null argument");
+  DDLB_CUDA(cudaSetDevice(s->device));
+  for (int p = 0; p < s->world; ++p) {
+    if (p == s->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, static_cast<const char*>(handles) + static_cast<size_t>(p) * DDLB_IPC_HANDLE_BYTES, sizeof(h));
+    cudaError_t e = cudaIpcOpenMemHandle(&s->base[p], h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      (void)cudaGetLastError();
+      return set_error("cudaIpcOpenMemHandle(rank %d): %s", p, cudaGetErrorString(e));
+    }
+    s->opened[p] = true;
+  }
+  return 0;
+}
+
+extern "C" int ddlb_symm_adopt_peer(ddlb_symm* s, int peer_rank, ddlb_symm* peer) {
+  using namespace ddlb;
+  if (s == nullptr || peer == nullptr || peer_rank < 0 || peer_rank >= s->world || peer_rank == s->rank)
+    return set_error("bad adopt_peer arguments");
+  s->base[peer_rank] = peer->base[peer->rank];
+  return 0;
+}
+
+extern "C" void* ddlb_symm_base(ddlb_symm* s, int rank) {
+  if (s == nullptr || rank < 0 || rank >= s->world) return nullptr;
+  return s->base[rank];
+}
+
+extern "C" int64_t ddlb_symm_bytes(ddlb_symm* s) { return s ? s->bytes : 0; }
+
+extern "C" int ddlb_symm_barrier(ddlb_symm* s, void* stream) {
+  using namespace ddlb;
+  if (s == nullptr) return set_error("null heap");
+  if (s->world == 1) return 0;
+  for (int p = 0; p < s->world; ++p)
+    if (s->base[p] == nullptr) return set_error("peer %d is not mapped", p);
+  s->barrier_epoch += 1;
+  uint32_t* sig[8] = {};
+  for (int p = 0; p < s->world; ++p) sig[p] = static_cast<uint32_t*>(s->base[p]);
+  barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(
+      sig[s->rank], nullptr, sig[0], sig[1], sig[2], sig[3], sig[4], sig[5], sig[6], sig[7], s->rank,
+      s->world, s->barrier_epoch);
+  DDLB_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int ddlb_symm_destroy(ddlb_symm* s) {
+  if (s == nullptr) return 0;
+  cudaSetDevice(s->device);
+  cudaDeviceSynchronize();
+  for (int p = 0; p < s->world; ++p)
+    if (s->opened[p] && s->base[p] != nullptr) cudaIpcCloseMemHandle(s->base[p]);
+  if (s->base[s->rank] != nullptr) cudaFree(s->base[s->rank]);
+  (void)cudaGetLastError();
+  delete s;
+  return 0;
+}
+
+extern "C" int ddlb_read_error_word(uint32_t out[4]) {
+  using namespace ddlb;
+  if (out == nullptr) return set_error("null argument");
+  DDLB_CUDA(cudaMemcpyFromSymbol(out, g_ddlb_error_word, 4 * sizeof(uint32_t)));
+  return 0;
+}
+
+// ------------------------------------------------------------------ topology
+extern "C" int ddlb_topology_json(char* out, int64_t cap, int64_t* needed) {
+  using namespace ddlb;
+  std::string js = "{";
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess) { (void)cudaGetLastError(); ndev = 0; }
+  int drv = 0, rt = 0;
+  cudaDriverGetVersion(&drv);
+  cudaRuntimeGetVersion(&rt);
+  (void)cudaGetLastError();
+  js += "\"driver_version\": " + std::to_string(drv) + ", \"runtime_version\": " + std::to_string(rt);
+  js += ", \"device_count\": " + std::to_string(ndev) + ", \"devices\": [";
+  for (int d = 0; d < ndev; ++d) {
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, d) != cudaSuccess) { (void)cudaGetLastError(); continue; }
+    int mc = 0;
+    {
+      // CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED through the driver entry point (no -lcuda link)
+      using AttrFn = CUresult (*)(int*, CUdevice_attribute, CUdevice);
+      void* sym = nullptr;
+      cudaDriverEntryPointQueryResult q;
+      if (cudaGetDriverEntryPoint("cuDeviceGetAttribute", &sym, cudaEnableDefault, &q) == cudaSuccess &&
+          q == cudaDriverEntryPointSuccess && sym != nullptr)
+        reinterpret_cast<AttrFn>(sym)(&mc, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, d);
+      (void)cudaGetLastError();
+    }
+    if (d) js += ", ";
+    js += "{\"index\": " + std::to_string(d) + ", \"name\": \"" + prop.name + "\"";
+    js += ", \"cc\": \"" + std::to_string(prop.major) + "." + std::to_string(prop.minor) + "\"";
+    js += ", \"sms\": " + std::to_string(prop.multiProcessorCount);
+    js += ", \"mem_bytes\": " + std::to_string(static_cast<long long>(prop.totalGlobalMem));
+    js += ", \"l2_bytes\": " + std::to_string(prop.l2CacheSize);
+    js += ", \"smem_per_block_optin\": " + std::to_string(static_cast<long long>(prop.sharedMemPerBlockOptin));
+    js += ", \"multicast_supported\": " + std::to_string(mc);
+    js += ", \"peers\": [";
+    bool first = true;
+    for (int q = 0; q < ndev; ++q) {
+      if (q == d) continue;
+      int can = 0, perf = -1, atom = 0;
+      cudaDeviceCanAccessPeer(&can, d, q);
+      cudaDeviceGetP2PAttribute(&perf, cudaDevP2PAttrPerformanceRank, d, q);
+      cudaDeviceGetP2PAttribute(&atom, cudaDevP2PAttrNativeAtomicSupported, d, q);
+      (void)cudaGetLastError();
+      if (!first) js += ", ";
+      first = false;
+      js += "{\"peer\": " + std::to_string(q) + ", \"access\": " + std::to_string(can) +
+            ", \"perf_rank\": " + std::to_string(perf) + ", \"native_atomics\": " + std::to_string(atom) + "}";
+    }
+    js += "]}";
+  }
+  js += "]}";
+  if (needed != nullptr) *needed = static_cast<int64_t>(js.size()) + 1;
+  if (out != nullptr && cap > 0) {
+    const size_t n = js.size() < static_cast<size_t>(cap - 1) ? js.size() : static_cast<size_t>(cap - 1);
+    memcpy(out, js.data(), n);
+    out[n] = '\0';
+  }
+  return 0;
+}

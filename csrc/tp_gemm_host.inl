@@ -1,0 +1,382 @@
+// Host side of the fused GEMM: config resolution, TMA tensor maps, launch.
+// Included by ddlb_b200.cu (unity build).
+
+namespace ddlb {
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) !=
+            cudaSuccess || qres != cudaDriverEntryPointSuccess || sym == nullptr) {
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    fn = reinterpret_cast<EncodeTiledFn>(sym);
+  }
+  return fn;
+}
+
+// rank-2/3 tiled map of 16-bit elements, 128-byte swizzle
+static int make_tmap(CUtensorMap* map, void* base, int rank, const uint64_t* dims,
+                     const uint64_t* strides_bytes, const uint32_t* box) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (fn == nullptr) return set_error("cuTensorMapEncodeTiled is unavailable (no CUDA driver?)");
+  cuuint64_t gdims[3];
+  cuuint64_t gstrides[2];
+  cuuint32_t gbox[3];
+  cuuint32_t estr[3] = {1, 1, 1};
+  for (int i = 0; i < rank; ++i) { gdims[i] = dims[i]; gbox[i] = box[i]; }
+  for (int i = 0; i + 1 < rank; ++i) gstrides[i] = strides_bytes[i];
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT16, static_cast<cuuint32_t>(rank), base, gdims,
+                  gstrides, gbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return set_error("cuTensorMapEncodeTiled failed with CUresult %d (base=%p rank=%d dims=%llu,%llu)",
+                     static_cast<int>(r), base, rank, static_cast<unsigned long long>(dims[0]),
+                     static_cast<unsigned long long>(dims[1]));
+  return 0;
+}
+
+struct Resolved {
+  int cta_group, block_n, group_m, grid, n_comm_ctas, chunk_rows;
+  int tile_m, part_rows, a_rows, kk;   // kk: contraction length seen by this kernel
+};
+
+static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
+  if (c.world < 1 || c.world > DDLB_MAX_WORLD || c.rank < 0 || c.rank >= c.world)
+    return set_error("bad rank/world %d/%d", c.rank, c.world);
+  if (c.mode < 0 || c.mode > 3) return set_error("bad mode %d", c.mode);
+  if (c.dtype != DDLB_DTYPE_F16 && c.dtype != DDLB_DTYPE_BF16) return set_error("bad dtype %d", c.dtype);
+  if (c.m <= 0 || c.n <= 0 || c.k <= 0) return set_error("bad shape");
+  if (c.m % c.world != 0) return set_error("m (%lld) must be divisible by world (%d)", (long long)c.m, c.world);
+  r.part_rows = static_cast<int>(c.m / c.world);
+  r.kk = static_cast<int>(c.mode == DDLB_MODE_RS ? c.k / c.world : c.k);
+  if (c.mode == DDLB_MODE_RS && c.k % c.world != 0)
+    return set_error("k (%lld) must be divisible by world (%d)", (long long)c.k, c.world);
+  if (r.kk % 8 != 0) return set_error("contraction length %d must be a multiple of 8 (16-byte rows)", r.kk);
+  if (c.n % 8 != 0) return set_error("n must be a multiple of 8 (16-byte rows)");
+  if (c.b_layout == DDLB_B_ROW_MAJOR_KN && c.n % 64 != 0)
+    return set_error("n (%lld) must be a multiple of 64 when B is [k,n] row-major", (long long)c.n);
+  r.a_rows = static_cast<int>(c.mode == DDLB_MODE_AG_AFTER ? r.part_rows : c.m);
+
+  const bool sharded_rows = c.mode != DDLB_MODE_PLAIN;   // tiles must not straddle shards
+  r.cta_group = c.cta_group;
+  if (r.cta_group == 0) r.cta_group = (!sharded_rows || r.part_rows % 256 == 0) ? 2 : 1;
+  if (r.cta_group != 1 && r.cta_group != 2) return set_error("cta_group must be 1 or 2");
+  r.tile_m = kBlockM * r.cta_group;
+  if (sharded_rows && r.part_rows % r.tile_m != 0)
+    return set_error("rows per rank (%d) must be a multiple of %d for the fused kernel", r.part_rows, r.tile_m);
+  r.block_n = c.block_n != 0 ? c.block_n : (c.n <= 128 ? 128 : 256);
+  if (r.block_n != 128 && r.block_n != 256) return set_error("block_n must be 128 or 256");
+
+  int dev = 0, sms = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess ||
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return set_error("cannot query the current CUDA device");
+  }
+  r.grid = c.num_sms > 0 ? (c.num_sms < sms ? c.num_sms : sms) : sms;
+  r.grid -= r.grid % r.cta_group;
+  if (r.grid < r.cta_group) return set_error("no SMs to launch on");
+
+  r.group_m = c.group_m > 0 ? c.group_m : 8;
+
+  r.n_comm_ctas = 0;
+  r.chunk_rows = r.part_rows;
+  if (c.mode == DDLB_MODE_AG_BEFORE || c.mode == DDLB_MODE_RS) {
+    int cr = c.chunk_rows;
+    if (cr <= 0) {
+      // auto: about 1 MiB of A per chunk (AG) / 4 tile rows (RS), dividing the shard evenly
+      const int mblks = r.part_rows / r.tile_m;
+      int want = c.mode == DDLB_MODE_AG_BEFORE
+                     ? static_cast<int>((1 << 20) / (static_cast<int64_t>(r.kk) * 2 * r.tile_m))
+                     : mblks;
+      if (want < 1) want = 1;
+      if (want > mblks) want = mblks;
+      while (mblks % want != 0) --want;
+      cr = want * r.tile_m;
+    }
+    if (cr % r.tile_m != 0 || r.part_rows % cr != 0)
+      return set_error("chunk_rows (%d) must be a multiple of %d and divide rows per rank (%d)", cr,
+                       r.tile_m, r.part_rows);
+    r.chunk_rows = cr;
+  }
+  if (c.mode == DDLB_MODE_AG_BEFORE && c.world > 1) {
+    int nc = c.n_comm_ctas > 0 ? c.n_comm_ctas : 16;
+    nc -= nc % r.cta_group;
+    if (nc < r.cta_group) nc = r.cta_group;
+    const int64_t chunk_bytes = static_cast<int64_t>(r.chunk_rows) * r.kk * 2;
+    while (nc > r.cta_group && (chunk_bytes % (static_cast<int64_t>(nc) * 16) != 0)) nc -= r.cta_group;
+    if (chunk_bytes % (static_cast<int64_t>(nc) * 16) != 0)
+      return set_error("chunk of %lld bytes cannot be split over %d comm CTAs", (long long)chunk_bytes, nc);
+    if (nc >= r.grid) return set_error("n_comm_ctas (%d) leaves no CTA for the GEMM", nc);
+    if (chunk_bytes > 0xffffffffll) return set_error("chunk too large");
+    r.n_comm_ctas = nc;
+  }
+  return 0;
+}
+
+}  // namespace ddlb
+
+struct ddlb_tp_gemm_plan {
+  ddlb::TpGemmParams params;
+  ddlb::Resolved res;
+  ddlb_tp_gemm_config cfg;
+  void (*kernel)(ddlb::TpGemmParams);
+  void (*emu_kernel)(const ddlb::TpGemmParams*, int);
+  int smem_bytes;
+  int stages;
+};
+
+namespace ddlb {
+
+template <int G, int BN, bool NM>
+static int bind_kernel(ddlb_tp_gemm_plan* plan) {
+  using Cfg = TpGemmCfg<G, BN>;
+  auto k = tp_gemm_kernel<G, BN, NM>;
+  plan->kernel = reinterpret_cast<void (*)(TpGemmParams)>(k);
+  auto ke = tp_gemm_emulated_kernel<G, BN, NM>;
+  plan->emu_kernel = ke;
+  plan->smem_bytes = Cfg::kSmemBytes;
+  plan->stages = Cfg::kStages;
+  cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(ke, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return set_error("cudaFuncSetAttribute(smem=%d): %s", Cfg::kSmemBytes, cudaGetErrorString(e));
+  }
+  if (G == 2) {
+    e = cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    if (e != cudaSuccess) (void)cudaGetLastError();
+  }
+  return 0;
+}
+
+static int select_kernel(ddlb_tp_gemm_plan* plan) {
+  const int g = plan->res.cta_group, bn = plan->res.block_n;
+  const bool nm = plan->cfg.b_layout == DDLB_B_ROW_MAJOR_KN;
+  if (g == 1 && bn == 256) return nm ? bind_kernel<1, 256, true>(plan) : bind_kernel<1, 256, false>(plan);
+  if (g == 2 && bn == 256) return nm ? bind_kernel<2, 256, true>(plan) : bind_kernel<2, 256, false>(plan);
+  if (g == 1 && bn == 128) return nm ? bind_kernel<1, 128, true>(plan) : bind_kernel<1, 128, false>(plan);
+  if (g == 2 && bn == 128) return nm ? bind_kernel<2, 128, true>(plan) : bind_kernel<2, 128, false>(plan);
+  return set_error("no kernel for cta_group=%d block_n=%d", g, bn);
+}
+
+}  // namespace ddlb
+
+extern "C" int64_t ddlb_tp_gemm_sig_words(const ddlb_tp_gemm_config* cfg) {
+  if (cfg == nullptr) return -1;
+  ddlb::Resolved r;
+  if (ddlb::resolve(*cfg, r) != 0) return -1;
+  int64_t words = ddlb::kSigChunk;
+  if (cfg->mode == DDLB_MODE_AG_BEFORE) words += static_cast<int64_t>(cfg->world) * (r.part_rows / r.chunk_rows);
+  if (cfg->mode == DDLB_MODE_RS) {
+    const int64_t nb = (cfg->n + r.block_n - 1) / r.block_n;
+    words += static_cast<int64_t>(cfg->world) * (r.part_rows / ddlb::kBlockM) * nb;
+  }
+  return (words + 63) / 64 * 64;
+}
+
+extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_plan** out) {
+  using namespace ddlb;
+  if (cfg == nullptr || out == nullptr) return set_error("null argument");
+  *out = nullptr;
+  Resolved r;
+  if (int rc = resolve(*cfg, r)) return rc;
+  const ddlb_tp_gemm_config& c = *cfg;
+  if (c.a == nullptr || c.b == nullptr || c.out[c.rank] == nullptr) return set_error("null a/b/out pointer");
+  if (c.world > 1 && c.mode != DDLB_MODE_PLAIN) {
+    if (c.sig_local == nullptr) return set_error("sig_local is required for fused modes");
+    for (int p = 0; p < c.world; ++p) {
+      if (p == c.rank) continue;
+      if (c.sig_peer[p] == nullptr) return set_error("sig_peer[%d] is null", p);
+      if (c.mode == DDLB_MODE_AG_BEFORE && c.peer_a[p] == nullptr) return set_error("peer_a[%d] is null", p);
+      if (c.mode != DDLB_MODE_AG_BEFORE && c.out[p] == nullptr) return set_error("out[%d] is null", p);
+    }
+    if (c.mode == DDLB_MODE_RS && c.stage_local == nullptr) return set_error("stage_local is null");
+  }
+
+  auto* plan = new ddlb_tp_gemm_plan();
+  plan->cfg = c;
+  plan->res = r;
+  if (int rc = select_kernel(plan)) { delete plan; return rc; }
+
+  TpGemmParams& p = plan->params;
+  memset(&p, 0, sizeof(p));
+  const uint64_t N = static_cast<uint64_t>(c.n), K = static_cast<uint64_t>(r.kk);
+  const int load_n = r.block_n / r.cta_group;
+  int rc = 0;
+  {  // A: [a_rows, K] row-major, box 64 x 128
+    const uint64_t dims[2] = {K, static_cast<uint64_t>(r.a_rows)};
+    const uint64_t strides[1] = {K * 2};
+    const uint32_t box[2] = {kBlockK, kBlockM};
+    rc = make_tmap(&p.tmA, c.a, 2, dims, strides, box);
+  }
+  if (rc == 0) {
+    if (c.b_layout == DDLB_B_ROW_MAJOR_KN) {  // [K, N]: 3-D view {64 n, K, N/64}
+      const uint64_t dims[3] = {64, K, N / 64};
+      const uint64_t strides[2] = {N * 2, 128};
+      const uint32_t box[3] = {64, kBlockK, static_cast<uint32_t>(load_n / 64)};
+      rc = make_tmap(&p.tmB, c.b, 3, dims, strides, box);
+    } else {                                  // [N, K]: box 64 x load_n
+      const uint64_t dims[2] = {K, N};
+      const uint64_t strides[1] = {K * 2};
+      const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(load_n)};
+      rc = make_tmap(&p.tmB, c.b, 2, dims, strides, box);
+    }
+  }
+  for (int d = 0; d < c.world && rc == 0; ++d) {
+    if (c.out[d] == nullptr) continue;
+    uint64_t rows;
+    if (c.mode == DDLB_MODE_RS) rows = d == c.rank ? r.part_rows : 2ull * c.world * r.part_rows;
+    else rows = static_cast<uint64_t>(c.m);
+    if ((c.mode == DDLB_MODE_PLAIN || c.mode == DDLB_MODE_AG_BEFORE) && d != c.rank) continue;
+    const uint64_t dims[2] = {N, rows};
+    const uint64_t strides[1] = {N * 2};
+    const uint32_t box[2] = {64, 32};
+    rc = make_tmap(&p.tmOut[d], c.out[d], 2, dims, strides, box);
+  }
+  if (rc != 0) { delete plan; return rc; }
+
+  p.mode = c.mode;
+  p.rank = c.rank;
+  p.world = c.world;
+  p.num_m_blocks = (r.a_rows + r.tile_m - 1) / r.tile_m;
+  p.num_n_blocks = static_cast<int>((c.n + r.block_n - 1) / r.block_n);
+  p.num_k_blocks = (r.kk + kBlockK - 1) / kBlockK;
+  p.group_m = r.group_m;
+  p.part_rows = r.part_rows;
+  p.out_n = static_cast<int>(c.n);
+  if (c.mode == DDLB_MODE_AG_BEFORE || c.mode == DDLB_MODE_RS) {
+    p.mblks_per_part = r.part_rows / r.tile_m;
+    p.chunk_mblks = r.chunk_rows / r.tile_m;
+  } else {
+    p.mblks_per_part = p.num_m_blocks;
+    p.chunk_mblks = p.num_m_blocks;
+  }
+  p.rot0 = c.mode == DDLB_MODE_RS ? 1 : 0;
+  p.n_comm_clusters = r.n_comm_ctas / r.cta_group;
+  p.idesc = make_idesc(c.dtype == DDLB_DTYPE_BF16 ? 1u : 0u, static_cast<uint32_t>(r.tile_m),
+                       static_cast<uint32_t>(r.block_n), false, c.b_layout == DDLB_B_ROW_MAJOR_KN);
+  p.epoch = 0;
+  p.local_a = static_cast<uint8_t*>(c.a);
+  for (int d = 0; d < c.world; ++d) {
+    p.peer_a[d] = static_cast<const uint8_t*>(c.peer_a[d]);
+    p.sig_peer[d] = c.sig_peer[d];
+  }
+  p.peer_a[c.rank] = static_cast<const uint8_t*>(c.a);
+  p.chunk_bytes = static_cast<uint32_t>(static_cast<int64_t>(r.chunk_rows) * r.kk * 2);
+  p.slice_bytes = r.n_comm_ctas > 0 ? p.chunk_bytes / r.n_comm_ctas : 0;
+  p.stage_local = static_cast<const uint8_t*>(c.stage_local);
+  p.rs_sig_off = kSigChunk;
+  p.rs_tiles_per_src = (r.part_rows / kBlockM) * p.num_n_blocks;
+  p.sig_local = c.sig_local;
+  p.sig_peer[c.rank] = c.sig_local;
+  *out = plan;
+  return 0;
+}
+
+extern "C" int ddlb_tp_gemm_run(ddlb_tp_gemm_plan* plan, uint32_t epoch, void* stream) {
+  using namespace ddlb;
+  if (plan == nullptr) return set_error("null plan");
+  plan->params.epoch = epoch;
+  cudaLaunchConfig_t lc;
+  memset(&lc, 0, sizeof(lc));
+  lc.gridDim = dim3(static_cast<unsigned>(plan->res.grid), 1, 1);
+  lc.blockDim = dim3(kNumThreads, 1, 1);
+  lc.dynamicSmemBytes = static_cast<size_t>(plan->smem_bytes);
+  lc.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = static_cast<unsigned>(plan->res.cta_group);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  lc.attrs = attr;
+  lc.numAttrs = 1;
+  void* args[1] = {&plan->params};
+  cudaError_t e = cudaLaunchKernelExC(&lc, reinterpret_cast<const void*>(plan->kernel), args);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return set_error("kernel launch failed: %s", cudaGetErrorString(e));
+  }
+  return 0;
+}
+
+extern "C" int ddlb_tp_gemm_info(const ddlb_tp_gemm_plan* plan, int32_t out[8]) {
+  if (plan == nullptr || out == nullptr) return ddlb::set_error("null argument");
+  out[0] = plan->res.grid;
+  out[1] = plan->res.cta_group;
+  out[2] = plan->smem_bytes;
+  out[3] = plan->res.cta_group;
+  out[4] = plan->res.block_n;
+  out[5] = plan->stages;
+  out[6] = plan->res.n_comm_ctas;
+  out[7] = plan->res.chunk_rows;
+  return 0;
+}
+
+extern "C" int ddlb_tp_gemm_destroy(ddlb_tp_gemm_plan* plan) {
+  delete plan;
+  return 0;
+}
+
+// Test helper: run `world` plans (one per emulated rank, all on the current device)
+// as ONE launch; see tp_gemm_emulated_kernel.
+extern "C" int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, uint32_t epoch,
+                                         void* stream) {
+  using namespace ddlb;
+  if (plans == nullptr || world < 1 || world > DDLB_MAX_WORLD) return set_error("bad arguments");
+  const ddlb_tp_gemm_plan* first = plans[0];
+  for (int r = 0; r < world; ++r) {
+    if (plans[r] == nullptr) return set_error("null plan %d", r);
+    if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group)
+      return set_error("emulated ranks must use the same kernel variant");
+  }
+  int dev = 0, sms = 0;
+  DDLB_CUDA(cudaGetDevice(&dev));
+  DDLB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int g = first->res.cta_group;
+  int clusters_per_rank = (sms / world) / g;
+  const int want = first->res.grid / g;            // honour a smaller num_sms request
+  if (first->cfg.num_sms > 0 && want < clusters_per_rank) clusters_per_rank = want;
+  if (clusters_per_rank <= first->params.n_comm_clusters)
+    return set_error("%d clusters per emulated rank leave none for the GEMM", clusters_per_rank);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  TpGemmParams* dparams = nullptr;
+  DDLB_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&dparams), sizeof(TpGemmParams) * world, st));
+  for (int r = 0; r < world; ++r) {
+    plans[r]->params.epoch = epoch;
+    DDLB_CUDA(cudaMemcpyAsync(dparams + r, &plans[r]->params, sizeof(TpGemmParams),
+                              cudaMemcpyHostToDevice, st));
+  }
+  cudaLaunchConfig_t lc;
+  memset(&lc, 0, sizeof(lc));
+  lc.gridDim = dim3(static_cast<unsigned>(clusters_per_rank * g * world), 1, 1);
+  lc.blockDim = dim3(kNumThreads, 1, 1);
+  lc.dynamicSmemBytes = static_cast<size_t>(first->smem_bytes);
+  lc.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = static_cast<unsigned>(g);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  lc.attrs = attr;
+  lc.numAttrs = 1;
+  const TpGemmParams* carg = dparams;
+  void* args[2] = {&carg, &clusters_per_rank};
+  cudaError_t e = cudaLaunchKernelExC(&lc, reinterpret_cast<const void*>(first->emu_kernel), args);
+  cudaFreeAsync(dparams, st);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return set_error("emulated launch failed: %s", cudaGetErrorString(e));
+  }
+  return 0;
+}

@@ -1,0 +1,529 @@
+// Persistent warp-specialised tcgen05 GEMM for sm_100a with the tensor-parallel
+// collectives fused into its tile schedule.
+//
+//   mode PLAIN      C[M,N]      = A[M,K] * B                        (world = 1 / compute ceiling)
+//   mode AG_BEFORE  C[m,N]      = allgather_rows(A)[m,K] * B        (tp_columnwise, gather inputs)
+//   mode AG_AFTER   C[m,N]      = allgather_rows(A_local * B)       (tp_columnwise, gather outputs)
+//   mode RS         C[m/d,N]    = reduce_scatter_rows(A_local * B)  (tp_rowwise)
+//
+// Replaces the reference's library call pairs: ncclAllGather + cuBLAS GEMM
+// (ddlb/primitives/TPColumnwise/pytorch.py:96-102) and cuBLAS GEMM +
+// ncclReduceScatter (ddlb/primitives/TPRowwise/pytorch.py:82-83), and the
+// stream-pipelined nvFuser/TE variants (TPColumnwise/fuser.py:16-146,
+// TPRowwise/fuser.py:15-169): their "algorithm/s/order" knobs are tile orders here.
+//
+// CTA roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one lane),
+// warp 2 = TMEM allocator, warps 4..7 = epilogue (one TMEM lane quadrant each).
+// In AG_BEFORE the first `n_comm_clusters` clusters do not compute: they pull the
+// peers' row shards over NVLink with bulk-async copies (global -> smem ring -> local
+// global) and publish per-chunk arrival counters that the GEMM producers wait on.
+//
+// Cross-GPU protocol: all flags are monotonic (value = epoch * arrivals) so
+// back-to-back launches never need a clearing pass; data that can be overwritten by
+// a peer running one launch ahead is double-buffered by epoch parity.
+#pragma once
+
+#include "ptx.cuh"
+
+namespace ddlb {
+
+constexpr int kBlockM = 128;   // rows per CTA (a cta_group::2 pair covers 256)
+constexpr int kBlockK = 64;    // 64 x 16-bit = one 128-byte swizzle row
+constexpr int kUmmaK = 16;
+constexpr int kNumThreads = 256;
+constexpr int kMaxWorld = 8;
+constexpr int kEpiBufBytes = 32 * 128;          // 32 rows x 64 cols x 2 B per warp buffer
+constexpr int kEpiBytes = 4 * 2 * kEpiBufBytes;  // 4 warps x double buffer
+constexpr int kSmemBudget = 193 * 1024;         // operand ring
+constexpr int kCommPiece = 16 * 1024;           // bytes per bulk copy of a comm CTA
+constexpr int kCommRing = 12;
+constexpr int kCommLag = 3;
+
+enum : int { kModePlain = 0, kModeAGBefore = 1, kModeAGAfter = 2, kModeRS = 3 };
+
+// word offsets inside a rank's signal block
+constexpr int kSigReady = 0;    // [src]   epoch written by src when its kernel started
+constexpr int kSigDone = 8;     // [src]   AG_AFTER: += 1 per CTA of src whose stores landed
+constexpr int kSigChunk = 16;   // [chunk] AG_BEFORE: += 1 per comm CTA slice copied
+// RS tile counters follow the chunk flags: [src][cta_tile] += 1 per epilogue warp
+
+struct TpGemmParams {
+  CUtensorMap tmA;
+  CUtensorMap tmB;
+  CUtensorMap tmOut[kMaxWorld];
+  int mode;
+  int rank, world;
+  int num_m_blocks;       // cluster tiles along M (of the A operand map)
+  int num_n_blocks;
+  int num_k_blocks;
+  int group_m;            // rasterisation: m-blocks per group (L2 reuse)
+  int mblks_per_part;     // cluster tiles per rank shard (AG_BEFORE / RS), else num_m_blocks
+  int chunk_mblks;        // cluster tiles per chunk (divides mblks_per_part)
+  int rot0;               // 0: own part first (AG), 1: own part last (RS)
+  int n_comm_clusters;    // AG_BEFORE only
+  int part_rows;          // rows per shard (m / world)
+  int out_n;              // N (elements per output row)
+  uint32_t idesc;
+  uint32_t epoch;
+  // AG_BEFORE
+  const uint8_t* peer_a[kMaxWorld];   // peers' gathered-A buffers (peer mapped)
+  uint8_t* local_a;                   // this rank's gathered-A buffer
+  uint32_t chunk_bytes;               // bytes of one chunk (chunk rows * K * 2)
+  uint32_t slice_bytes;               // chunk_bytes / comm CTAs
+  // RS
+  const uint8_t* stage_local;         // [2][world][part_rows][N] partials pushed by peers
+  int rs_sig_off;                     // word offset of the RS counters in a signal block
+  int rs_tiles_per_src;               // (part_rows / 128) * num_n_blocks
+  // signals
+  uint32_t* sig_local;
+  uint32_t* sig_peer[kMaxWorld];
+};
+
+template <int kCtaGroup, int kBlockN>
+struct TpGemmCfg {
+  static constexpr int kTileM = kBlockM * kCtaGroup;
+  static constexpr int kLoadN = kBlockN / kCtaGroup;            // B columns staged per CTA
+  static constexpr int kStageA = kBlockM * kBlockK * 2;
+  static constexpr int kStageB = kLoadN * kBlockK * 2;
+  static constexpr int kStageBytes = kStageA + kStageB;
+  static constexpr int kStagesRaw = kSmemBudget / kStageBytes;
+  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kTmemCols = 2 * kBlockN;
+  static constexpr int kBarBytes = 512;
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kEpiBytes + kBarBytes;
+  static_assert(kStages >= 3, "operand ring too shallow");
+  static_assert(kCommRing * kCommPiece <= kStages * kStageBytes, "comm ring does not fit");
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory budget exceeded");
+};
+
+struct TileCoord {
+  int m_blk;   // cluster tile index along M in the A operand map
+  int n_blk;
+  int part;    // owning / source rank of these rows
+  int chunk;   // chunk index inside the part
+};
+
+// Linear tile index -> tile, identical in every role. Grouped rasterisation over an
+// arrival-ordered sequence of m-blocks.
+__device__ __forceinline__ TileCoord tile_coord(const TpGemmParams& p, int t) {
+  const int per_group = p.group_m * p.num_n_blocks;
+  const int group = t / per_group;
+  const int within = t - group * per_group;
+  const int first = group * p.group_m;
+  const int rows_in_group = min(p.group_m, p.num_m_blocks - first);
+  const int n_blk = within / rows_in_group;
+  const int ord = first + (within - n_blk * rows_in_group);
+  TileCoord c;
+  c.n_blk = n_blk;
+  if (p.mode == kModePlain || p.mode == kModeAGAfter) {
+    c.m_blk = ord;
+    c.part = p.rank;
+    c.chunk = 0;
+    return c;
+  }
+  const int per_stage = p.world * p.chunk_mblks;
+  const int stage = ord / per_stage;
+  const int rem = ord - stage * per_stage;
+  const int pi = rem / p.chunk_mblks;
+  const int w = rem - pi * p.chunk_mblks;
+  int part = p.rank + p.rot0 + pi;
+  part = part >= p.world ? part - p.world : part;
+  part = part >= p.world ? part - p.world : part;
+  c.part = part;
+  c.chunk = stage;
+  c.m_blk = part * p.mblks_per_part + stage * p.chunk_mblks + w;
+  return c;
+}
+
+__device__ __forceinline__ uint32_t pack2(float lo, float hi, bool bf16) {
+  uint32_t out;
+  if (bf16) {
+    const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    memcpy(&out, &v, 4);
+  } else {
+    const __half2 v = __floats2half2_rn(lo, hi);
+    memcpy(&out, &v, 4);
+  }
+  return out;
+}
+
+// v[0..8) hold fp32 bit patterns; add 8 packed 16-bit values to them in fp32.
+__device__ __forceinline__ void add_packed8(uint32_t* v, uint4 raw, bool bf16) {
+  const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 f;
+    if (bf16) {
+      __nv_bfloat162 h;
+      memcpy(&h, &w[i], 4);
+      f = __bfloat1622float2(h);
+    } else {
+      __half2 h;
+      memcpy(&h, &w[i], 4);
+      f = __half22float2(h);
+    }
+    v[2 * i] = __float_as_uint(__uint_as_float(v[2 * i]) + f.x);
+    v[2 * i + 1] = __float_as_uint(__uint_as_float(v[2 * i + 1]) + f.y);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// communication CTAs (AG_BEFORE): pull peers' chunks into the local gathered-A
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void comm_cta_loop(const TpGemmParams& p, uint8_t* ring, uint32_t bar_base,
+                                              int ci, int nci) {
+  // bar_base: kCommRing mbarriers (8 B each), already initialised with count 1
+  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
+  const int n_chunks = chunks_per_part * (p.world - 1);
+  const uint32_t pieces_per_slice = (p.slice_bytes + kCommPiece - 1) / kCommPiece;
+  const int total = n_chunks * static_cast<int>(pieces_per_slice);
+  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
+
+  if (ci == 0 && threadIdx.x < static_cast<unsigned>(p.world) &&
+      static_cast<int>(threadIdx.x) != p.rank) {
+    // tell every peer that this rank's shard is final for this epoch
+    st_release_sys(p.sig_peer[threadIdx.x] + kSigReady + p.rank, p.epoch);
+  }
+  if (threadIdx.x != 0) return;
+
+  uint32_t ready_mask = 1u << p.rank;
+  auto piece_addr = [&](int i, size_t& off, uint32_t& bytes, int& part, int& chunk_in_part,
+                        bool& last) {
+    const int c = i / static_cast<int>(pieces_per_slice);        // chunk in fetch order
+    const uint32_t pc = i - c * pieces_per_slice;
+    const int stage = c / (p.world - 1);
+    const int pi = c - stage * (p.world - 1);
+    int src = p.rank + 1 + pi;
+    src = src >= p.world ? src - p.world : src;
+    part = src;
+    chunk_in_part = stage;
+    const uint32_t in_slice = pc * kCommPiece;
+    bytes = min(static_cast<uint32_t>(kCommPiece), p.slice_bytes - in_slice);
+    off = static_cast<size_t>(src) * part_bytes + static_cast<size_t>(stage) * p.chunk_bytes +
+          static_cast<size_t>(ci) * p.slice_bytes + in_slice;
+    last = (pc + 1 == pieces_per_slice);
+  };
+  auto issue_load = [&](int i) {
+    size_t off; uint32_t bytes; int part, cip; bool last;
+    piece_addr(i, off, bytes, part, cip, last);
+    if (!(ready_mask & (1u << part))) {
+      wait_flag_ge<true>(p.sig_local + kSigReady + part, p.epoch);
+      ready_mask |= 1u << part;
+    }
+    const int slot = i % kCommRing;
+    const uint32_t bar = bar_base + slot * 8;
+    mbar_arrive_expect_tx(bar, bytes);
+    bulk_load(smem_u32(ring + slot * kCommPiece), p.peer_a[part] + off, bytes, bar);
+  };
+
+  const int prefill = total < kCommRing ? total : kCommRing;
+  for (int i = 0; i < prefill; ++i) issue_load(i);
+  for (int i = 0; i < total + kCommLag; ++i) {
+    if (i < total) {
+      size_t off; uint32_t bytes; int part, cip; bool last;
+      piece_addr(i, off, bytes, part, cip, last);
+      const int slot = i % kCommRing;
+      mbar_wait(bar_base + slot * 8, (i / kCommRing) & 1);
+      bulk_store(p.local_a + off, smem_u32(ring + slot * kCommPiece), bytes);
+      bulk_commit();
+      if (last) {
+        bulk_wait<0>();           // this slice of the chunk is in local memory
+        fence_proxy_async();
+        red_add_release_gpu(p.sig_local + kSigChunk + part * chunks_per_part + cip, 1u);
+      }
+    }
+    const int j = i - kCommLag;
+    if (j >= 0 && j + kCommRing < total) {
+      if (i < total) bulk_wait_read<kCommLag>();
+      else bulk_wait_read<0>();
+      issue_load(j + kCommRing);
+    }
+  }
+  bulk_wait<0>();
+}
+
+// ---------------------------------------------------------------------------
+// the kernel
+// ---------------------------------------------------------------------------
+template <int kCtaGroup, int kBlockN, bool kBNMajor>
+__device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cluster,
+                                             const int nclusters) {
+  using Cfg = TpGemmCfg<kCtaGroup, kBlockN>;
+  constexpr int kStages = Cfg::kStages;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint8_t* smem_ops = smem;                                   // [stage]{A, B}
+  uint8_t* smem_epi = smem + kStages * Cfg::kStageBytes;      // [warp][2][4 KB]
+  uint8_t* smem_bar = smem_epi + kEpiBytes;
+  const uint32_t bar_full = smem_u32(smem_bar);               // [kStages] (also comm ring, <= 12)
+  const uint32_t bar_empty = bar_full + 12 * 8;               // [kStages]
+  const uint32_t bar_tfull = bar_empty + 12 * 8;              // [2]
+  const uint32_t bar_tempty = bar_tfull + 2 * 8;              // [2]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem_bar + 28 * 8);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = kCtaGroup == 2 ? cluster_ctarank() : 0u;
+  const bool is_comm = (p.mode == kModeAGBefore) && cluster < p.n_comm_clusters;
+  const bool bf16 = ((p.idesc >> 7) & 7u) == 1u;
+
+  // ------------------------------------------------------------------ setup
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&p.tmA);
+    prefetch_tmap(&p.tmB);
+    prefetch_tmap(&p.tmOut[p.rank]);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < 12; ++s) {
+      mbar_init(bar_full + s * 8, 1);
+      mbar_init(bar_empty + s * 8, 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(bar_tfull + a * 8, 1);
+      mbar_init(bar_tempty + a * 8, 4 * kCtaGroup);
+    }
+    fence_mbar_init();
+  }
+  __syncwarp();
+  if (warp == 2) {
+    tmem_alloc<kCtaGroup>(smem_u32(tmem_ptr_smem), Cfg::kTmemCols);
+    tmem_relinquish<kCtaGroup>();
+  }
+  tc_fence_before();
+  if constexpr (kCtaGroup == 2) cluster_sync(); else __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+  const int gemm_cluster = cluster - (p.mode == kModeAGBefore ? p.n_comm_clusters : 0);
+  const int gemm_clusters = nclusters - (p.mode == kModeAGBefore ? p.n_comm_clusters : 0);
+
+  if (is_comm) {
+    // -------------------------------------------------------- comm role
+    comm_cta_loop(p, smem_ops, bar_full, cluster * kCtaGroup + static_cast<int>(cta_rank),
+                  p.n_comm_clusters * kCtaGroup);
+  } else if (warp == 0 && lane == 0) {
+    // -------------------------------------------------------- TMA producer
+    const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
+    const uint32_t chunk_target = p.epoch * static_cast<uint32_t>(p.n_comm_clusters * kCtaGroup);
+    const uint32_t full_leader = kCtaGroup == 2 ? mapa(bar_full, 0) : bar_full;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
+      const TileCoord tc = tile_coord(p, t);
+      if (p.mode == kModeAGBefore && tc.part != p.rank) {
+        wait_flag_ge<false>(p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk,
+                            chunk_target);
+        fence_proxy_async();      // flag acquired by the generic proxy, data read by TMA
+      }
+      const int m0 = tc.m_blk * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
+      const int n0 = tc.n_blk * kBlockN + static_cast<int>(cta_rank) * Cfg::kLoadN;
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        mbar_wait(bar_empty + stage * 8, phase ^ 1u);
+        uint8_t* sa = smem_ops + stage * Cfg::kStageBytes;
+        uint8_t* sb = sa + Cfg::kStageA;
+        if (kCtaGroup == 1 || cta_rank == 0)
+          mbar_arrive_expect_tx(bar_full + stage * 8, Cfg::kStageBytes * kCtaGroup);
+        const uint32_t fb = full_leader + stage * 8;
+        tma_load_2d<kCtaGroup>(smem_u32(sa), &p.tmA, fb, kb * kBlockK, m0);
+        if constexpr (kBNMajor)
+          tma_load_3d<kCtaGroup>(smem_u32(sb), &p.tmB, fb, 0, kb * kBlockK, n0 / 64);
+        else
+          tma_load_2d<kCtaGroup>(smem_u32(sb), &p.tmB, fb, kb * kBlockK, n0);
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp == 1 && lane == 0 && cta_rank == 0) {
+    // -------------------------------------------------------- MMA issuer
+    // K-major operand: 8-row groups 1024 B apart, k-step = 32 B inside the swizzle row.
+    // N-major B: 64-column blocks 8 KB apart (LBO), 8-k-row groups 1024 B apart (SBO),
+    //            k-step = 16 rows * 128 B.
+    constexpr uint32_t kBLbo = kBNMajor ? 64 * kBlockK * 2 : 16;
+    constexpr uint32_t kBStep = kBNMajor ? (kUmmaK * 128) >> 4 : (kUmmaK * 2) >> 4;
+    int stage = 0;
+    uint32_t phase = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
+      mbar_wait(bar_tempty + acc * 8, acc_phase ^ 1u);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kBlockN);
+      for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+        mbar_wait(bar_full + stage * 8, phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem_ops + stage * Cfg::kStageBytes);
+        const uint64_t adesc = make_smem_desc_sw128(sa, 16, 1024);
+        const uint64_t bdesc = make_smem_desc_sw128(sa + Cfg::kStageA, kBLbo, 1024);
+#pragma unroll
+        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+          umma_f16<kCtaGroup>(tmem_d, adesc + static_cast<uint64_t>(k * ((kUmmaK * 2) >> 4)),
+                              bdesc + static_cast<uint64_t>(k * kBStep), p.idesc,
+                              static_cast<uint32_t>((kb | k) != 0));
+        }
+        umma_commit<kCtaGroup>(bar_empty + stage * 8);     // smem slot reusable when MMAs retire
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
+      }
+      umma_commit<kCtaGroup>(bar_tfull + acc * 8);         // accumulator ready for the epilogue
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+  } else if (warp >= 4) {
+    // -------------------------------------------------------- epilogue
+    const int q = warp & 3;                                 // TMEM lane quadrant
+    uint8_t* ebuf = smem_epi + q * 2 * kEpiBufBytes;
+    const uint32_t tempty_leader = kCtaGroup == 2 ? mapa(bar_tempty, 0) : bar_tempty;
+    int buf = 0;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    uint32_t* pending_sig = nullptr;                        // RS: counter of the previous pushed tile
+    const uint32_t parity = p.epoch & 1u;
+    for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
+      const TileCoord tc = tile_coord(p, t);
+      const int row_cta = tc.m_blk * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
+      const int row0 = row_cta + q * 32;
+      const int n0 = tc.n_blk * kBlockN;
+      mbar_wait(bar_tfull + acc * 8, acc_phase);
+      tc_fence_after();
+
+      const bool rs_push = p.mode == kModeRS && tc.part != p.rank;
+      const bool rs_own = p.mode == kModeRS && tc.part == p.rank;
+      int out_row = row0;
+      int local_row = 0;
+      int cta_tile = 0;
+      if (p.mode == kModeRS) {
+        local_row = row0 - tc.part * p.part_rows;           // row inside the owner's shard
+        cta_tile = ((row_cta - tc.part * p.part_rows) / kBlockM) * p.num_n_blocks + tc.n_blk;
+        out_row = rs_push ? (static_cast<int>(parity) * p.world + p.rank) * p.part_rows + local_row
+                          : local_row;
+      } else if (p.mode == kModeAGAfter) {
+        out_row = p.rank * p.part_rows + row0;
+      }
+      if (pending_sig != nullptr) {
+        // previous tile's remote stores: complete them, then publish its counter
+        if (lane == 0) {
+          bulk_wait<0>();
+          fence_proxy_async();
+          red_add_release_sys(pending_sig, 1u);
+        }
+        pending_sig = nullptr;
+      }
+      if (rs_own) {
+        if (lane < p.world && lane != p.rank)
+          wait_flag_ge<true>(p.sig_local + p.rs_sig_off + lane * p.rs_tiles_per_src + cta_tile,
+                             4u * p.epoch);
+        __syncwarp();
+      }
+
+#pragma unroll 1
+      for (int c = 0; c < kBlockN / 64; ++c) {
+        uint32_t v[64];
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                               static_cast<uint32_t>(acc * kBlockN + c * 64);
+        tmem_ld_32x32b_x32(taddr, &v[0]);
+        tmem_ld_32x32b_x32(taddr + 32, &v[32]);
+        tmem_ld_wait();
+
+        if (rs_own) {
+          const int lr = local_row + lane;
+          for (int s = 0; s < p.world; ++s) {
+            if (s == p.rank) continue;
+            const size_t row = static_cast<size_t>(parity * p.world + s) * p.part_rows + lr;
+            const uint4* src = reinterpret_cast<const uint4*>(
+                p.stage_local + (row * p.out_n + n0 + c * 64) * 2);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint4 raw = __ldcg(src + j);
+              add_packed8(&v[8 * j], raw, bf16);
+            }
+          }
+        }
+
+        uint32_t packed[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          packed[i] = pack2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]), bf16);
+
+        if (lane == 0) bulk_wait_read<1>();     // the store that last used this buffer has read it
+        __syncwarp();
+        const uint32_t sbase = smem_u32(ebuf + buf * kEpiBufBytes);
+        const uint32_t srow = sbase + lane * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const uint32_t dst = srow + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(packed[4 * j]),
+                       "r"(packed[4 * j + 1]), "r"(packed[4 * j + 2]), "r"(packed[4 * j + 3])
+                       : "memory");
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          if (p.mode == kModeAGAfter) {
+            for (int d = 0; d < p.world; ++d) tma_store_2d(&p.tmOut[d], sbase, n0 + c * 64, out_row);
+          } else {
+            tma_store_2d(&p.tmOut[tc.part], sbase, n0 + c * 64, out_row);
+          }
+          bulk_commit();
+        }
+        buf ^= 1;
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (kCtaGroup == 2 && cta_rank != 0) mbar_arrive_cluster(tempty_leader + acc * 8);
+        else mbar_arrive(bar_tempty + acc * 8);
+      }
+      if (rs_push)
+        pending_sig = p.sig_peer[tc.part] + p.rs_sig_off + p.rank * p.rs_tiles_per_src + cta_tile;
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+    if (lane == 0) {
+      bulk_wait<0>();
+      if (pending_sig != nullptr) {
+        fence_proxy_async();
+        red_add_release_sys(pending_sig, 1u);
+      }
+    }
+    if (p.mode == kModeAGAfter && p.world > 1) {
+      // every CTA tells every peer that its share of C has landed, then waits for
+      // all CTAs of all peers so that C is complete when this kernel ends
+      if (lane == 0) { fence_proxy_async(); fence_acq_rel_sys(); }
+      named_bar_sync(1, 128);
+      if (warp == 4 && lane < p.world && lane != p.rank) {
+        red_add_release_sys(p.sig_peer[lane] + kSigDone + p.rank, 1u);
+        wait_flag_ge<true>(p.sig_local + kSigDone + lane,
+                           p.epoch * static_cast<uint32_t>(nclusters * kCtaGroup));
+      }
+    }
+  }
+
+  // ---------------------------------------------------------------- teardown
+  __syncwarp();
+  tc_fence_before();
+  if constexpr (kCtaGroup == 2) cluster_sync(); else __syncthreads();
+  if (warp == 2) tmem_dealloc<kCtaGroup>(tmem_base, Cfg::kTmemCols);
+}
+
+// One rank per process / GPU: parameters in the kernel parameter space.
+template <int kCtaGroup, int kBlockN, bool kBNMajor>
+__global__ void __launch_bounds__(kNumThreads, 1)
+tp_gemm_kernel(const __grid_constant__ TpGemmParams p) {
+  const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
+  const int nclusters = kCtaGroup == 2 ? static_cast<int>(num_clusters_x()) : static_cast<int>(gridDim.x);
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor>(p, cluster, nclusters);
+}
+
+// Several ranks emulated by ONE launch on one GPU (tests): the grid is split into
+// `world` equal groups of clusters, group r runs rank r's parameter block. All
+// CTAs of one launch are co-resident (grid <= SM count), so ranks that wait on
+// each other make progress, which separate launches on one GPU cannot guarantee.
+template <int kCtaGroup, int kBlockN, bool kBNMajor>
+__global__ void __launch_bounds__(kNumThreads, 1)
+tp_gemm_emulated_kernel(const TpGemmParams* __restrict__ plist, int clusters_per_rank) {
+  const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
+  const int vr = cluster / clusters_per_rank;
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor>(plist[vr], cluster - vr * clusters_per_rank,
+                                             clusters_per_rank);
+}
+
+}  // namespace ddlb

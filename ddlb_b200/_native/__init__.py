@@ -1,0 +1,107 @@
+"""ctypes binding of ``libddlb_b200.so`` (C ABI in ``include/ddlb_b200.h``).
+
+The library is built in-tree (``python -m ddlb_b200._native.build``) and loaded on
+first use. If it is missing the load fails loudly: there is no silent PyTorch
+fallback for the product kernels.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import (POINTER, Structure, byref, c_char_p, c_int, c_int32, c_int64, c_uint32,
+                    c_void_p)
+from typing import Optional
+
+MAX_WORLD = 8
+IPC_HANDLE_BYTES = 64
+MODE_PLAIN, MODE_AG_BEFORE, MODE_AG_AFTER, MODE_RS = 0, 1, 2, 3
+DTYPE_F16, DTYPE_BF16 = 0, 1
+B_KN, B_NK = 0, 1
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libddlb_b200.so")
+_lib: Optional[ctypes.CDLL] = None
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+class TpGemmConfig(Structure):
+    _fields_ = [
+        ("mode", c_int32), ("dtype", c_int32), ("b_layout", c_int32), ("cta_group", c_int32),
+        ("block_n", c_int32), ("group_m", c_int32), ("num_sms", c_int32), ("n_comm_ctas", c_int32),
+        ("rank", c_int32), ("world", c_int32), ("chunk_rows", c_int32), ("reserved", c_int32),
+        ("m", c_int64), ("n", c_int64), ("k", c_int64),
+        ("a", c_void_p), ("b", c_void_p),
+        ("out", c_void_p * MAX_WORLD), ("peer_a", c_void_p * MAX_WORLD),
+        ("stage_local", c_void_p),
+        ("sig_local", c_void_p), ("sig_peer", c_void_p * MAX_WORLD),
+    ]
+
+
+def lib() -> ctypes.CDLL:
+    """Load (building first if the sources are newer and nvcc is available)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if os.environ.get("DDLB_NO_AUTOBUILD", "0") != "1":
+        try:
+            from . import build as _build
+            if _build.is_stale():
+                _build.build()
+        except Exception as exc:  # no nvcc on the box: use the shipped .so if present
+            if not os.path.exists(LIB_PATH):
+                raise NativeError(f"libddlb_b200.so is missing and could not be built: {exc}")
+    if not os.path.exists(LIB_PATH):
+        raise NativeError(
+            f"{LIB_PATH} not found; run `python -m ddlb_b200._native.build` (needs nvcc)")
+    L = ctypes.CDLL(LIB_PATH)
+    L.ddlb_last_error.restype = c_char_p
+    L.ddlb_version.restype = c_int
+    L.ddlb_topology_json.argtypes = [c_char_p, c_int64, POINTER(c_int64)]
+    L.ddlb_symm_create.argtypes = [c_int, c_int, c_int, c_int64, POINTER(c_void_p)]
+    L.ddlb_symm_export.argtypes = [c_void_p, c_void_p]
+    L.ddlb_symm_open_peers.argtypes = [c_void_p, c_void_p]
+    L.ddlb_symm_adopt_peer.argtypes = [c_void_p, c_int, c_void_p]
+    L.ddlb_symm_base.argtypes = [c_void_p, c_int]
+    L.ddlb_symm_base.restype = c_void_p
+    L.ddlb_symm_bytes.argtypes = [c_void_p]
+    L.ddlb_symm_bytes.restype = c_int64
+    L.ddlb_symm_barrier.argtypes = [c_void_p, c_void_p]
+    L.ddlb_symm_destroy.argtypes = [c_void_p]
+    L.ddlb_tp_gemm_sig_words.argtypes = [POINTER(TpGemmConfig)]
+    L.ddlb_tp_gemm_sig_words.restype = c_int64
+    L.ddlb_tp_gemm_create.argtypes = [POINTER(TpGemmConfig), POINTER(c_void_p)]
+    L.ddlb_tp_gemm_run.argtypes = [c_void_p, c_uint32, c_void_p]
+    L.ddlb_tp_gemm_info.argtypes = [c_void_p, POINTER(c_int32 * 8)]
+    L.ddlb_tp_gemm_destroy.argtypes = [c_void_p]
+    L.ddlb_tp_gemm_run_emulated.argtypes = [POINTER(c_void_p), c_int, c_uint32, c_void_p]
+    L.ddlb_read_error_word.argtypes = [POINTER(c_uint32 * 4)]
+    _lib = L
+    return L
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = lib().ddlb_last_error().decode(errors="replace")
+        raise NativeError(f"{what}: {msg}" if what else msg)
+
+
+def loaded() -> bool:
+    return _lib is not None
+
+
+def topology_json() -> str:
+    L = lib()
+    need = c_int64(0)
+    check(L.ddlb_topology_json(None, 0, byref(need)), "topology")
+    buf = ctypes.create_string_buffer(need.value + 16)
+    check(L.ddlb_topology_json(buf, len(buf), byref(need)), "topology")
+    return buf.value.decode()
+
+
+def read_error_word():
+    word = (c_uint32 * 4)()
+    check(lib().ddlb_read_error_word(byref(word)), "read_error_word")
+    return list(word)

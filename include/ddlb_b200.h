@@ -1,0 +1,106 @@
+/* C ABI of libddlb_b200.so — the native layer of the B200 tensor-parallel
+ * primitive library. Every function returns 0 on success and a non-zero code on
+ * failure; ddlb_last_error() then describes the failure (thread-local string).
+ *
+ * Pointers named "peer" are device addresses of ANOTHER rank's memory mapped into
+ * this process (see ddlb_symm_*). Streams are cudaStream_t handles passed as void*.
+ */
+#ifndef DDLB_B200_H_
+#define DDLB_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DDLB_MAX_WORLD 8
+
+const char* ddlb_last_error(void);
+int ddlb_version(void);
+
+/* ---------------------------------------------------------------- topology
+ * JSON description of the visible devices: name, SM count, memory, peer-access
+ * matrix, P2P attributes, multicast (NVLS) support. No counterpart in the
+ * reference beyond torch.cuda.set_device (ddlb/communicator.py:56-60).
+ * Writes at most `cap` bytes (NUL terminated); returns bytes needed in *needed. */
+int ddlb_topology_json(char* out, int64_t cap, int64_t* needed);
+
+/* ----------------------------------------------------------- symmetric heap
+ * One cudaMalloc arena per rank, exported with cudaIpc and mapped by every peer
+ * (replaces NCCL communicator setup, ddlb/primitives/TPColumnwise/pytorch.py:53-59).
+ * The first DDLB_SIGNAL_BYTES of the arena are zero-initialised signal pads. */
+#define DDLB_IPC_HANDLE_BYTES 64
+typedef struct ddlb_symm ddlb_symm;
+
+int ddlb_symm_create(int device, int rank, int world, int64_t bytes, ddlb_symm** out);
+int ddlb_symm_export(ddlb_symm* s, void* handle_out /* DDLB_IPC_HANDLE_BYTES */);
+/* handles: world * DDLB_IPC_HANDLE_BYTES, indexed by rank (own entry ignored) */
+int ddlb_symm_open_peers(ddlb_symm* s, const void* handles);
+/* single-process emulation (tests): adopt another heap of the same process as peer */
+int ddlb_symm_adopt_peer(ddlb_symm* s, int peer_rank, ddlb_symm* peer);
+void* ddlb_symm_base(ddlb_symm* s, int rank);   /* base address of rank's arena as seen here */
+int64_t ddlb_symm_bytes(ddlb_symm* s);
+int ddlb_symm_destroy(ddlb_symm* s);
+
+/* Device-side barrier over the signal pads (replaces dist.barrier /
+ * the dummy all_reduce of ddlb/benchmark.py:134-137, ddlb/communicator.py:74).
+ * Asynchronous on `stream`; every rank must call it the same number of times. */
+int ddlb_symm_barrier(ddlb_symm* s, void* stream);
+
+/* --------------------------------------------------------------- fused GEMM */
+enum { DDLB_MODE_PLAIN = 0, DDLB_MODE_AG_BEFORE = 1, DDLB_MODE_AG_AFTER = 2, DDLB_MODE_RS = 3 };
+enum { DDLB_DTYPE_F16 = 0, DDLB_DTYPE_BF16 = 1 };
+enum { DDLB_B_ROW_MAJOR_KN = 0, DDLB_B_ROW_MAJOR_NK = 1 };
+
+typedef struct ddlb_tp_gemm_config {
+  int32_t mode;          /* DDLB_MODE_* */
+  int32_t dtype;         /* DDLB_DTYPE_* (inputs and output; fp32 accumulate) */
+  int32_t b_layout;      /* DDLB_B_ROW_MAJOR_KN: B is [k,n]; _NK: B is [n,k] (pre-transposed) */
+  int32_t cta_group;     /* 1 or 2 (tcgen05 cta_group), 0 = auto */
+  int32_t block_n;       /* 128 or 256, 0 = auto */
+  int32_t group_m;       /* rasterisation group, 0 = auto */
+  int32_t num_sms;       /* CTAs to launch, 0 = all SMs */
+  int32_t n_comm_ctas;   /* AG_BEFORE: CTAs that pull peer shards, 0 = auto */
+  int32_t rank, world;
+  int32_t chunk_rows;    /* rows per pipeline chunk inside a shard, 0 = auto */
+  int32_t reserved;
+  int64_t m, n, k;       /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
+  /* PLAIN:     a = A[m,k]                 out[rank] = C[m,n]
+   * AG_BEFORE: a = gathered A[m,k] (own shard rows already in place), peer_a[r] = rank r's
+   *            gathered buffer, out[rank] = C[m,n]
+   * AG_AFTER:  a = A_local[m/d,k]         out[r] = rank r's C[m,n]
+   * RS:        a = A_local[m,k/d], b = B_local[k/d,n], out[rank] = C_shard[m/d,n],
+   *            out[r != rank] = rank r's staging [2][d][m/d][n], stage_local = own staging */
+  void* a;
+  void* b;
+  void* out[DDLB_MAX_WORLD];
+  void* peer_a[DDLB_MAX_WORLD];
+  void* stage_local;
+  uint32_t* sig_local;                  /* this op's signal words (zero-initialised) */
+  uint32_t* sig_peer[DDLB_MAX_WORLD];   /* the same block on every peer */
+} ddlb_tp_gemm_config;
+
+typedef struct ddlb_tp_gemm_plan ddlb_tp_gemm_plan;
+
+/* number of uint32 signal words the op needs for this config */
+int64_t ddlb_tp_gemm_sig_words(const ddlb_tp_gemm_config* cfg);
+int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_plan** out);
+/* epoch: 1, 2, 3, ... incremented by the caller on every launch, identical on all ranks */
+int ddlb_tp_gemm_run(ddlb_tp_gemm_plan* plan, uint32_t epoch, void* stream);
+/* resolved launch shape: {grid, cluster, smem_bytes, cta_group, block_n, stages, n_comm_ctas,
+ * chunk_rows}; */
+int ddlb_tp_gemm_info(const ddlb_tp_gemm_plan* plan, int32_t out[8]);
+int ddlb_tp_gemm_destroy(ddlb_tp_gemm_plan* plan);
+/* Tests on one GPU: run `world` plans (one per emulated rank, all created on the current
+ * device, same kernel variant) as ONE launch whose CTAs are split between the ranks, so
+ * ranks that wait on each other are co-resident. No counterpart in the reference. */
+int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, uint32_t epoch, void* stream);
+
+/* device-side error word set by a kernel that timed out waiting ({code, block, aux0, aux1}) */
+int ddlb_read_error_word(uint32_t out[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDLB_B200_H_ */
