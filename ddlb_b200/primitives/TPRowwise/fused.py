@@ -1,0 +1,82 @@
+"""``fused``: the product implementation of ``tp_rowwise`` — GEMM and ReduceScatter
+in ONE hand-written sm_100a kernel per rank (``csrc/tp_gemm_sm100.cuh``).
+
+Replaces cuBLAS + ``ncclReduceScatter`` (reference
+``ddlb/primitives/TPRowwise/pytorch.py:70-85``) and the nvFuser pipelines
+(``ddlb/primitives/TPRowwise/fuser.py:15-169``). Partial-output tiles leave TMEM,
+are rounded once to the output type and stored with TMA straight into the owning
+rank's staging buffer over NVLink; the owner's own tiles are scheduled last and
+their epilogue adds the staged partials in fp32. No full ``[m,n]`` partial is ever
+written to local HBM and no separate reduction kernel runs.
+
+``algorithm``: ``default`` / ``p2p_pipeline`` visit owners in ring order
+(rank+1 ... rank) with one chunk per owner; ``coll_pipeline`` splits every
+owner's rows into ``s`` slabs and visits slab j of all owners before slab j+1.
+"""
+from __future__ import annotations
+
+from .tp_rowwise import TPRowwise
+
+
+class FusedTPRowwise(TPRowwise):
+    DEFAULT_OPTIONS = {
+        "algorithm": "default",
+        "s": 2,
+        "cta_group": 0,
+        "block_n": 0,
+        "transport": "p2p",
+    }
+    ALLOWED_VALUES = {
+        "algorithm": ["default", "coll_pipeline", "p2p_pipeline"],
+        "s": (1, 1024),
+        "cta_group": [0, 1, 2],
+        "block_n": [0, 128, 256],
+        "transport": ["auto", "p2p"],
+    }
+
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
+        import torch
+        from ...ops.tp_gemm import FusedGemmReduceScatter
+
+        comm = self.communicator
+        if not comm.is_cuda:
+            raise RuntimeError("the fused implementation needs a CUDA device (sm_100a)")
+        if self.torch_dtype not in (torch.float16, torch.bfloat16):
+            raise ValueError(
+                f"fused tp_rowwise supports float16/bfloat16 (got {self.dtype}); "
+                "use the pytorch baseline for other dtypes")
+        d = comm.world_size
+        rows = self.m // d
+        chunk_rows = 0
+        if self.options["algorithm"] == "coll_pipeline":
+            s = int(self.options["s"])
+            if rows % s != 0:
+                raise ValueError(f"rows per rank ({rows}) must be divisible by s ({s})")
+            chunk_rows = rows // s
+        heap = None
+        if d > 1:
+            comm.init_process_group()
+            heap = comm.symmetric_heap(2 * self.m * self.n * 2 + (64 << 20))
+        self.op = FusedGemmReduceScatter(
+            heap, comm.rank, d, self.m, self.n, self.k, self.torch_dtype, self.A, self.B,
+            chunk_rows=chunk_rows, cta_group=int(self.options["cta_group"]),
+            block_n=int(self.options["block_n"]))
+        torch.cuda.synchronize()
+        if d > 1:
+            heap.barrier()
+            torch.cuda.synchronize()
+
+    def run(self):
+        return self.op.run()
+
+    def device_barrier(self) -> None:
+        if self.communicator.world_size > 1:
+            self.communicator.symmetric_heap().barrier()
+
+    @property
+    def gpu_launches(self) -> int:
+        return self.op.launches
+
+    def close(self) -> None:
+        self.op.close()

@@ -1,0 +1,61 @@
+"""tcgen05 GEMM kernel vs a plain PyTorch fp32 reference of the same op (1 GPU)."""
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(out, ref, k):
+    import torch
+    err = (out.float() - ref).abs()
+    tol = 2e-2 * (k ** 0.5) + 1e-2 * ref.abs()
+    bad = int((~(err <= tol)).sum())
+    assert bad == 0, f"{bad}/{err.numel()} elements out of tolerance, max err {err.max().item()}"
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
+@pytest.mark.parametrize("block_n", [128, 256])
+@pytest.mark.parametrize("b_is_nk", [False, True])
+@pytest.mark.parametrize("dtype", ["bfloat16", "float16"])
+@pytest.mark.parametrize("shape", [(256, 256, 64), (384, 320, 200), (1024, 1152, 512)])
+def test_plain_gemm(cta_group, block_n, b_is_nk, dtype, shape):
+    import torch
+    from ddlb_b200.ops.tp_gemm import plain_gemm_plan
+    from ddlb_b200 import _native as N
+    torch.manual_seed(1)
+    m, n, k = shape
+    dt = getattr(torch, dtype)
+    a = torch.randn(m, k, device="cuda", dtype=dt)
+    b_kn = torch.randn(k, n, device="cuda", dtype=dt)
+    b = b_kn.t().contiguous() if b_is_nk else b_kn
+    plan, out = plain_gemm_plan(a, b, b_is_nk=b_is_nk, cta_group=cta_group, block_n=block_n)
+    out.fill_(float("nan"))
+    plan.run()
+    plan.run()                      # back-to-back launches reuse barriers/TMEM correctly
+    torch.cuda.synchronize()
+    assert N.loaded()
+    _check(out, a.float() @ b_kn.float(), k)
+
+
+def test_gemm_matches_reference_tolerance_headline_shape():
+    """Uniform [-1,1) inputs and the reference's atol = 1e-3 * k."""
+    import torch
+    from ddlb_b200.ops.tp_gemm import gemm
+    torch.manual_seed(42)
+    m, n, k = 8192, 1024, 1024
+    a = (2 * torch.rand(m, k, device="cuda") - 1).bfloat16()
+    b = (2 * torch.rand(k, n, device="cuda") - 1).bfloat16()
+    out = gemm(a, b)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(out.float(), a.float() @ b.float(), rtol=0, atol=1e-3 * k)
+
+
+def test_unsupported_shapes_fail_loudly():
+    import torch
+    from ddlb_b200.ops.tp_gemm import plain_gemm_plan
+    from ddlb_b200._native import NativeError
+    a = torch.randn(128, 64, device="cuda", dtype=torch.bfloat16)
+    b = torch.randn(64, 100, device="cuda", dtype=torch.bfloat16)    # n % 64 != 0
+    with pytest.raises(NativeError):
+        plain_gemm_plan(a, b)
+    with pytest.raises(TypeError):
+        plain_gemm_plan(a.float(), b.float())
