@@ -461,7 +461,8 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
           if (p.mode == kModeAGAfter) {
             for (int d = 0; d < p.world; ++d) tma_store_2d(&p.tmOut[d], sbase, n0 + c * 64, out_row);
           } else {
-            tma_store_2d(&p.tmOut[tc.part], sbase, n0 + c * 64, out_row);
+            // RS: the owner's staging (or own shard) map; otherwise this rank's C
+            tma_store_2d(&p.tmOut[p.mode == kModeRS ? tc.part : p.rank], sbase, n0 + c * 64, out_row);
           }
           bulk_commit();
         }
