@@ -1,0 +1,407 @@
+#!/usr/bin/env python3
+"""Headline benchmark (driver contract).
+
+    python bench.py --gpus N --steps K --warmup W [--impl ours|reference]
+
+N > 1 is launched by the driver with ``python -m torch.distributed.run --nproc-per-node N
+... bench.py --gpus N ...`` (one rank per GPU). Rank 0 prints ONE JSON line.
+
+Metric (BASELINE.json): tensor-parallel AllGather->GEMM throughput, ``2*m*n*k / t``
+TFLOP/s as in the reference's ``Throughput (TFLOPS)`` column
+(``ddlb/benchmark.py:209-214``), on the headline config ``tp_columnwise m=65536 n=1024
+k=1024 bf16``; a "step" is one ``run()`` of the primitive (one fused kernel launch per
+rank for our arm; ncclAllGather + cuBLAS for the reference arm). The global problem
+is fixed as N grows ("strong" scaling). ``secondary`` reports the GEMM->ReduceScatter
+headline config (``tp_rowwise m=8192 n=1024 k=8192 fp16``) measured the same way.
+
+``--impl reference`` runs the UNMODIFIED reference from ``baseline/_ref`` through its
+own ``ddlb.cli.run_benchmark`` (``pytorch;backend=nccl;order=AG_before``, CUDA-event
+timing) and prints the same JSON shape with ``"impl": "reference"``.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+HEADLINE = {"primitive": "tp_columnwise", "m": 65536, "n": 1024, "k": 1024, "dtype": "bfloat16"}
+SECONDARY = {"primitive": "tp_rowwise", "m": 8192, "n": 1024, "k": 8192, "dtype": "float16"}
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Sample SM clock / throttle reasons of one GPU through NVML while the timed
+    region runs (a thread; ``torch.cuda.synchronize`` releases the GIL)."""
+
+    REASONS = {
+        0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap",
+        0x8: "hw_slowdown", 0x10: "sync_boost", 0x20: "sw_thermal_slowdown",
+        0x40: "hw_thermal_slowdown", 0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting",
+    }
+
+    def __init__(self, index: int, period_s: float = 0.004):
+        self.index, self.period = index, period_s
+        self.samples, self.reason_bits = [], 0
+        self.max_mhz = None
+        self._stop = threading.Event()
+        self._thread = None
+        self._nvml = None
+        self._handle = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nvml = pynvml
+            self._handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._handle, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self._nvml = None
+
+    def sample(self) -> None:
+        if self._nvml is None:
+            return
+        try:
+            n = self._nvml
+            self.samples.append(n.nvmlDeviceGetClockInfo(self._handle, n.NVML_CLOCK_SM))
+            self.reason_bits |= int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self._handle))
+        except Exception:
+            pass
+
+    def _loop(self) -> None:
+        while not self._stop.is_set():
+            self.sample()
+            time.sleep(self.period)
+
+    def start(self) -> None:
+        self.samples, self.reason_bits = [], 0
+        self._stop.clear()
+        self.sample()
+        if self._nvml is not None:
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+
+    def stop(self) -> dict:
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join()
+            self._thread = None
+        self.sample()
+        reasons = [name for bit, name in self.REASONS.items()
+                   if self.reason_bits & bit and name != "gpu_idle"]
+        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
+                "sm_max_mhz": self.max_mhz, "reasons": reasons, "samples": len(self.samples)}
+
+
+def _physical_gpu_index(local_rank: int) -> int:
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return int(vis.split(",")[local_rank])
+        except Exception:
+            pass
+    return local_rank
+
+
+# -------------------------------------------------------------------------- our arm
+def _timed_steps(impl, comm, steps: int):
+    """EXACTLY ``steps`` runs between barrier+sync brackets, CUDA events; ms per step."""
+    import torch
+    comm.barrier()
+    torch.cuda.synchronize()
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    out = None
+    for _ in range(steps):
+        out = impl.run()
+    end.record()
+    torch.cuda.synchronize()
+    comm.barrier()
+    return start.elapsed_time(end) / steps, out
+
+
+def _e2e_steps(impl, comm, steps: int, warmup: int):
+    """End to end through the public API: every step copies this rank's input shard from
+    pinned host memory to the device, runs the primitive, and reads a result row back."""
+    import torch
+    shard_dev = impl.A                                    # device tensor the kernel reads
+    host_in = torch.empty(shard_dev.shape, dtype=shard_dev.dtype).pin_memory()
+    host_in.copy_(shard_dev)
+    probe = impl.run()
+    host_out = torch.empty(probe.shape[1], dtype=probe.dtype).pin_memory()
+    h2d = host_in.numel() * host_in.element_size()
+    d2h = host_out.numel() * host_out.element_size()
+
+    def step():
+        shard_dev.copy_(host_in, non_blocking=True)
+        out = impl.run()
+        host_out.copy_(out[0], non_blocking=True)
+
+    for _ in range(warmup):
+        step()
+    comm.barrier()
+    torch.cuda.synchronize()
+    start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    for _ in range(steps):
+        step()
+    end.record()
+    torch.cuda.synchronize()
+    comm.barrier()
+    return start.elapsed_time(end) / steps, h2d, d2h
+
+
+def _measure_ours(cfg: dict, steps: int, warmup: int, with_e2e: bool, sampler):
+    import torch
+    from ddlb_b200.primitives.registry import load_impl_class
+    impl_cls = load_impl_class(cfg["primitive"], "fused")
+    impl = impl_cls(m=cfg["m"], n=cfg["n"], k=cfg["k"], dtype=cfg["dtype"])
+    comm = impl.communicator
+    for _ in range(max(warmup, 3)):
+        impl.run()
+    torch.cuda.synchronize()
+    launches0 = impl.gpu_launches
+    if sampler is not None:
+        sampler.start()
+    ms, out = _timed_steps(impl, comm, steps)
+    clocks = sampler.stop() if sampler is not None else None
+    launches = impl.gpu_launches - launches0
+    ms = max(comm.all_reduce_max([ms]))
+    valid = True
+    try:
+        impl.validate(out)
+    except Exception as exc:
+        valid = False
+        print(f"[bench] validation failed: {str(exc).splitlines()[0]}", file=sys.stderr)
+    res = {"ms_per_step": ms, "gpu_launches": launches, "valid": valid, "clocks": clocks,
+           "plan": dict(impl.op.plan.info) if getattr(impl.op, "plan", None) else {},
+           "flops_per_gpu": impl.flops_per_gpu(), "comm_bytes_per_gpu": impl.comm_bytes_per_gpu()}
+    if with_e2e:
+        e_ms, h2d, d2h = _e2e_steps(impl, comm, steps, max(warmup, 3))
+        e_ms = max(comm.all_reduce_max([e_ms]))
+        res["e2e"] = {"ms_per_step": e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h}
+    impl.close()
+    return res
+
+
+def run_ours(args) -> dict:
+    os.environ.setdefault("DDLB_SYMM_HEAP_BYTES", str(1 << 30))
+    import torch
+    from ddlb_b200.communicator import Communicator
+    from ddlb_b200.utils.roofline import measured_peaks, roofline_ms, NVLINK_MEASURED_GBS
+
+    comm = Communicator()
+    if comm.world_size != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE is {comm.world_size}: launch with "
+                         f"torch.distributed.run --nproc-per-node {args.gpus}")
+    if comm.world_size > 1:
+        comm.init_process_group()
+    sampler = ClockSampler(_physical_gpu_index(comm.local_rank))
+    head = _measure_ours(HEADLINE, args.steps, args.warmup, True, sampler)
+    sec = _measure_ours(SECONDARY, args.steps, args.warmup, False, None)
+
+    def tflops(cfg, ms):
+        return 2.0 * cfg["m"] * cfg["n"] * cfg["k"] / (ms * 1e9)
+
+    roof = roofline_ms(head["flops_per_gpu"], head["comm_bytes_per_gpu"], HEADLINE["dtype"])
+    roof_meas = roofline_ms(head["flops_per_gpu"], head["comm_bytes_per_gpu"], HEADLINE["dtype"],
+                            link_gbs=NVLINK_MEASURED_GBS)
+    sec_roof = roofline_ms(sec["flops_per_gpu"], sec["comm_bytes_per_gpu"], SECONDARY["dtype"])
+    peaks = measured_peaks()
+    out = {
+        "metric": "tp_columnwise_tflops", "value": tflops(HEADLINE, head["ms_per_step"]),
+        "unit": "TFLOP/s (2*m*n*k/t, whole job)", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "impl": "ours", "valid": head["valid"],
+        "config": {"model": "tp_columnwise AllGather->GEMM m=65536 n=1024 k=1024",
+                   "global_batch": HEADLINE["m"], "seq_len": HEADLINE["k"],
+                   "parallelism": f"tp{args.gpus}", "order": "AG_before",
+                   "implementation": "fused (one sm_100a kernel per rank)",
+                   "l2": "working set (A 128 MiB + C 128 MiB) exceeds the 126 MB L2; no flush",
+                   "kernel": head["plan"]},
+        "clocks": head["clocks"],
+        "gpu_launches": head["gpu_launches"],
+        "e2e": {"value": tflops(HEADLINE, head["e2e"]["ms_per_step"]),
+                "unit": "TFLOP/s (2*m*n*k/t, whole job)",
+                "ms_per_step": head["e2e"]["ms_per_step"],
+                "h2d_bytes_per_step": head["e2e"]["h2d_bytes_per_step"],
+                "d2h_bytes_per_step": head["e2e"]["d2h_bytes_per_step"]},
+        "roofline": {"t_roof_ms": roof, "pct_of_roofline": 100.0 * roof / head["ms_per_step"],
+                     "t_roof_ms_measured_link": roof_meas,
+                     "pct_of_roofline_measured_link": 100.0 * roof_meas / head["ms_per_step"],
+                     "gemm_peak_tflops": peaks["bf16_tflops"], "peaks_source": peaks["source"]},
+        "secondary": {"metric": "tp_rowwise_tflops",
+                      "config": "tp_rowwise GEMM->ReduceScatter m=8192 n=1024 k=8192 fp16",
+                      "value": tflops(SECONDARY, sec["ms_per_step"]),
+                      "ms_per_step": sec["ms_per_step"], "valid": sec["valid"],
+                      "gpu_launches": sec["gpu_launches"],
+                      "pct_of_roofline": 100.0 * sec_roof / sec["ms_per_step"]},
+    }
+    comm.shutdown()
+    return out if comm.rank == 0 else {}
+
+
+# -------------------------------------------------------------------- reference arm
+def _ensure_reference():
+    ref = os.path.join(ROOT, "baseline", "_ref")
+    if os.path.isdir(os.path.join(ref, "ddlb")):
+        return ref, None
+    src = "/root/reference"
+    if not os.path.isdir(src):
+        return None, "baseline/_ref is missing and /root/reference is not present on this box"
+    import shutil
+    import tempfile
+    tmp = tempfile.mkdtemp(prefix="ddlb_ref_")
+    copy = os.path.join(tmp, "reference")
+    shutil.copytree(src, copy)
+    cmd = [sys.executable, "-m", "pip", "install", "--no-index", "--no-build-isolation",
+           "--no-deps", "--find-links", "/opt/wheelhouse", "--target", ref, copy]
+    proc = subprocess.run(cmd, capture_output=True, text=True)
+    if proc.returncode != 0:
+        return None, "pip install of the reference failed: " + proc.stderr.strip().splitlines()[-1][:200]
+    return ref, None
+
+
+def _reference_case(ddlb_cli, cfg: dict, steps: int, warmup: int, csv_path: str, rank: int):
+    import csv
+    impl_opts = ({"backend": "nccl", "order": "AG_before"} if cfg["primitive"] == "tp_columnwise"
+                 else {"backend": "nccl"})
+    config = {"benchmark": {
+        "primitive": cfg["primitive"], "m": cfg["m"], "n": cfg["n"], "k": cfg["k"],
+        "dtype": cfg["dtype"], "validate": False, "num_iterations": steps,
+        "num_warmups": warmup, "output_csv": csv_path,
+        "time_measurement_backend": "cuda_event", "barrier_at_each_iteration": True,
+        "implementations": {"pytorch": [impl_opts]}}}
+    ddlb_cli.run_benchmark(config)
+    if rank != 0:
+        return None
+    with open(csv_path) as fh:
+        rows = list(csv.DictReader(fh))
+    row = rows[-1]
+    return {"ms_per_step": float(row["mean_time (ms)"]), "tflops": float(row["Throughput (TFLOPS)"]),
+            "label": row["implementation"]}
+
+
+def _arm_watchdog(seconds: float, payload: dict) -> None:
+    """The reference's parent blocks forever on ``result_queue.get()`` when its child dies
+    before posting a row (``ddlb/benchmark.py:369``). Never let that hang the driver:
+    after ``seconds`` report the arm as unavailable, stop our own children and exit 0."""
+    def fire():
+        import multiprocessing as mp
+        try:
+            for child in mp.active_children():
+                child.terminate()
+        except Exception:
+            pass
+        if int(os.environ.get("RANK", "0")) == 0:
+            os.write(1 if not hasattr(_arm_watchdog, "fd") else _arm_watchdog.fd,
+                     (json.dumps(payload) + "\n").encode())
+        os._exit(0)
+    timer = threading.Timer(seconds, fire)
+    timer.daemon = True
+    timer.start()
+
+
+def run_reference(args) -> dict:
+    try:
+        import torch
+        if not torch.cuda.is_available():
+            return {"impl": "reference", "unavailable": "no CUDA device: the reference's "
+                    "Communicator requires one (ddlb/communicator.py:56-60)"}
+    except Exception as exc:
+        return {"impl": "reference", "unavailable": f"torch import failed: {exc}"}
+    ref, why = _ensure_reference()
+    if ref is None:
+        return {"impl": "reference", "unavailable": why}
+    _arm_watchdog(float(os.environ.get("DDLB_REFERENCE_TIMEOUT", "900")),
+                  {"impl": "reference", "unavailable": "reference run did not finish in time "
+                   "(its parent hangs if a child dies before posting a row)"})
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        return {"impl": "reference", "unavailable": f"--gpus {args.gpus} but WORLD_SIZE={world}"}
+    # the reference reads Open MPI / SLURM variables only (ddlb/envs.py:50-67)
+    os.environ.update({"OMPI_COMM_WORLD_RANK": str(rank), "OMPI_COMM_WORLD_SIZE": str(world),
+                       "OMPI_COMM_WORLD_LOCAL_RANK": str(local_rank),
+                       "OMPI_COMM_WORLD_LOCAL_SIZE": os.environ.get("LOCAL_WORLD_SIZE", str(world)),
+                       "DDLB_MASTER_ADDR": "127.0.0.1",
+                       "DDLB_MASTER_PORT": str(int(os.environ.get("MASTER_PORT", "29500")) + 307)})
+    shims = os.path.join(ROOT, "baseline", "shims")
+    extra = [ref, shims]
+    try:
+        import matplotlib  # noqa: F401
+        extra = [ref]
+    except Exception:
+        pass
+    for path in reversed(extra):
+        sys.path.insert(0, path)
+    os.environ["PYTHONPATH"] = os.pathsep.join(extra + [os.environ.get("PYTHONPATH", "")])
+    # the reference prints progress on stdout; keep stdout for the single JSON line
+    sys.stdout.flush()
+    saved = os.dup(1)
+    _arm_watchdog.fd = saved
+    os.dup2(2, 1)
+    sampler = ClockSampler(_physical_gpu_index(local_rank), period_s=0.02)
+    try:
+        import ddlb.cli.benchmark as ddlb_cli
+        import tempfile
+        tmp = tempfile.mkdtemp(prefix="ddlb_ref_run_")
+        sampler.start()
+        head = _reference_case(ddlb_cli, HEADLINE, args.steps, args.warmup,
+                               os.path.join(tmp, "head.csv"), rank)
+        clocks = sampler.stop()
+        sec = _reference_case(ddlb_cli, SECONDARY, args.steps, args.warmup,
+                              os.path.join(tmp, "sec.csv"), rank)
+    except Exception as exc:
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        return {"impl": "reference", "unavailable": f"{type(exc).__name__}: {str(exc)[:200]}"}
+    sys.stdout.flush()
+    os.dup2(saved, 1)
+    if rank != 0:
+        return {}
+    return {
+        "metric": "tp_columnwise_tflops", "value": head["tflops"],
+        "unit": "TFLOP/s (2*m*n*k/t, whole job)", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "impl": "reference",
+        "config": {"model": "tp_columnwise AllGather->GEMM m=65536 n=1024 k=1024",
+                   "global_batch": HEADLINE["m"], "seq_len": HEADLINE["k"],
+                   "parallelism": f"tp{args.gpus}", "order": "AG_before",
+                   "implementation": "reference ddlb.cli.run_benchmark, " + head["label"],
+                   "timing": "reference's own loop: cuda_event, barrier each iteration, "
+                             "mean over iterations, max over ranks",
+                   "l2": "working set exceeds L2; no flush"},
+        "clocks": clocks, "gpu_launches": 0,
+        "secondary": {"metric": "tp_rowwise_tflops",
+                      "config": "tp_rowwise GEMM->ReduceScatter m=8192 n=1024 k=8192 fp16",
+                      "value": sec["tflops"], "ms_per_step": sec["ms_per_step"]},
+    }
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawTextHelpFormatter)
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    result = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if result:
+        print(json.dumps(result), flush=True)
+
+
+if __name__ == "__main__":
+    main()
