@@ -275,6 +275,7 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   p.peer_a[c.rank] = static_cast<const uint8_t*>(c.a);
   p.chunk_bytes = static_cast<uint32_t>(static_cast<int64_t>(r.chunk_rows) * r.kk * 2);
   p.slice_bytes = r.n_comm_ctas > 0 ? p.chunk_bytes / r.n_comm_ctas : 0;
+  p.comm_push = c.comm_pull ? 0 : 1;
   p.stage_local = static_cast<const uint8_t*>(c.stage_local);
   p.rs_sig_off = kSigChunk;
   p.rs_tiles_per_src = (r.part_rows / kBlockM) * p.num_n_blocks;

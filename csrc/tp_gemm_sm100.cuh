@@ -37,7 +37,7 @@ constexpr int kEpiBytes = 4 * 2 * kEpiBufBytes;  // 4 warps x double buffer
 constexpr int kSmemBudget = 193 * 1024;         // operand ring
 constexpr int kCommPiece = 16 * 1024;           // bytes per bulk copy of a comm CTA
 constexpr int kCommRing = 12;
-constexpr int kCommLag = 3;
+constexpr int kCommLag = 4;
 
 enum : int { kModePlain = 0, kModeAGBefore = 1, kModeAGAfter = 2, kModeRS = 3 };
 
@@ -70,6 +70,7 @@ struct TpGemmParams {
   uint8_t* local_a;                   // this rank's gathered-A buffer
   uint32_t chunk_bytes;               // bytes of one chunk (chunk rows * K * 2)
   uint32_t slice_bytes;               // chunk_bytes / comm CTAs
+  int comm_push;                      // 1: push own shard to peers, 0: pull peers' shards
   // RS
   const uint8_t* stage_local;         // [2][world][part_rows][N] partials pushed by peers
   int rs_sig_off;                     // word offset of the RS counters in a signal block
@@ -218,6 +219,9 @@ __device__ __forceinline__ void comm_cta_loop(const TpGemmParams& p, uint8_t* ri
 
   const int prefill = total < kCommRing ? total : kCommRing;
   for (int i = 0; i < prefill; ++i) issue_load(i);
+  // Store pipeline kCommLag groups deep. Group i is piece i's store (an empty group in the
+  // tail), so after committing group i "at most kCommLag pending" means piece i-kCommLag is
+  // in local memory: publish its chunk counter if it closed a chunk, recycle its ring slot.
   for (int i = 0; i < total + kCommLag; ++i) {
     if (i < total) {
       size_t off; uint32_t bytes; int part, cip; bool last;
@@ -225,18 +229,105 @@ __device__ __forceinline__ void comm_cta_loop(const TpGemmParams& p, uint8_t* ri
       const int slot = i % kCommRing;
       mbar_wait(bar_base + slot * 8, (i / kCommRing) & 1);
       bulk_store(p.local_a + off, smem_u32(ring + slot * kCommPiece), bytes);
-      bulk_commit();
+    }
+    bulk_commit();
+    const int j = i - kCommLag;
+    if (j >= 0) {
+      bulk_wait<kCommLag>();
+      size_t off; uint32_t bytes; int part, cip; bool last;
+      piece_addr(j, off, bytes, part, cip, last);
       if (last) {
-        bulk_wait<0>();           // this slice of the chunk is in local memory
         fence_proxy_async();
         red_add_release_gpu(p.sig_local + kSigChunk + part * chunks_per_part + cip, 1u);
       }
+      if (j + kCommRing < total) issue_load(j + kCommRing);
     }
-    const int j = i - kCommLag;
-    if (j >= 0 && j + kCommRing < total) {
-      if (i < total) bulk_wait_read<kCommLag>();
-      else bulk_wait_read<0>();
-      issue_load(j + kCommRing);
+  }
+  bulk_wait<0>();
+}
+
+// ---------------------------------------------------------------------------
+// communication CTAs (AG_BEFORE, push transport): every rank writes its own shard
+// into all peers' gathered-A buffers. A piece is read ONCE from local memory into
+// shared memory and stored to the d-1 peers from there; remote stores are posted,
+// so a slot is recycled as soon as the stores have read it (short lag) while the
+// chunk counters on the peers are bumped only when the stores have completed
+// (long lag) - neither waits for a round trip on the critical path.
+// ---------------------------------------------------------------------------
+constexpr int kPushReadLag = 3;
+constexpr int kPushDoneLag = 8;
+
+__device__ __forceinline__ void comm_cta_push_loop(const TpGemmParams& p, uint8_t* ring,
+                                                   uint32_t bar_base, int ci, int nci) {
+  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
+  const uint32_t pieces_per_slice = (p.slice_bytes + kCommPiece - 1) / kCommPiece;
+  const int total = chunks_per_part * static_cast<int>(pieces_per_slice);
+  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
+
+  if (ci == 0 && threadIdx.x < static_cast<unsigned>(p.world) &&
+      static_cast<int>(threadIdx.x) != p.rank) {
+    // this rank's previous launch is over: peers may overwrite its gathered buffer
+    st_release_sys(p.sig_peer[threadIdx.x] + kSigReady + p.rank, p.epoch);
+  }
+  if (threadIdx.x != 0) return;
+
+  auto piece_addr = [&](int i, size_t& off, uint32_t& bytes, int& chunk, bool& last) {
+    chunk = i / static_cast<int>(pieces_per_slice);
+    const uint32_t pc = i - chunk * pieces_per_slice;
+    const uint32_t in_slice = pc * kCommPiece;
+    bytes = min(static_cast<uint32_t>(kCommPiece), p.slice_bytes - in_slice);
+    off = static_cast<size_t>(p.rank) * part_bytes + static_cast<size_t>(chunk) * p.chunk_bytes +
+          static_cast<size_t>(ci) * p.slice_bytes + in_slice;
+    last = (pc + 1 == pieces_per_slice);
+  };
+  auto issue_load = [&](int i) {
+    size_t off; uint32_t bytes; int chunk; bool last;
+    piece_addr(i, off, bytes, chunk, last);
+    const int slot = i % kCommRing;
+    const uint32_t bar = bar_base + slot * 8;
+    mbar_arrive_expect_tx(bar, bytes);
+    bulk_load(smem_u32(ring + slot * kCommPiece), p.local_a + off, bytes, bar);
+  };
+
+  const int prefill = total < kCommRing ? total : kCommRing;
+  for (int i = 0; i < prefill; ++i) issue_load(i);
+  for (int d = 1; d < p.world; ++d) {
+    int peer = p.rank + d;
+    peer = peer >= p.world ? peer - p.world : peer;
+    wait_flag_ge<true>(p.sig_local + kSigReady + peer, p.epoch);
+  }
+  for (int i = 0; i < total + kPushDoneLag; ++i) {
+    if (i < total) {
+      size_t off; uint32_t bytes; int chunk; bool last;
+      piece_addr(i, off, bytes, chunk, last);
+      const int slot = i % kCommRing;
+      mbar_wait(bar_base + slot * 8, (i / kCommRing) & 1);
+      const uint32_t src = smem_u32(ring + slot * kCommPiece);
+      for (int d = 1; d < p.world; ++d) {
+        int peer = p.rank + d;
+        peer = peer >= p.world ? peer - p.world : peer;
+        bulk_store(const_cast<uint8_t*>(p.peer_a[peer]) + off, src, bytes);
+      }
+    }
+    bulk_commit();
+    const int jr = i - kPushReadLag;             // stores of piece jr have read their slot
+    if (jr >= 0 && jr + kCommRing < total) {
+      bulk_wait_read<kPushReadLag>();
+      issue_load(jr + kCommRing);
+    }
+    const int jd = i - kPushDoneLag;             // stores of piece jd have completed
+    if (jd >= 0) {
+      size_t off; uint32_t bytes; int chunk; bool last;
+      piece_addr(jd, off, bytes, chunk, last);
+      if (last) {
+        bulk_wait<kPushDoneLag>();
+        fence_proxy_async();
+        for (int d = 1; d < p.world; ++d) {
+          int peer = p.rank + d;
+          peer = peer >= p.world ? peer - p.world : peer;
+          red_add_release_sys(p.sig_peer[peer] + kSigChunk + p.rank * chunks_per_part + chunk, 1u);
+        }
+      }
     }
   }
   bulk_wait<0>();
@@ -302,8 +393,12 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
 
   if (is_comm) {
     // -------------------------------------------------------- comm role
-    comm_cta_loop(p, smem_ops, bar_full, cluster * kCtaGroup + static_cast<int>(cta_rank),
-                  p.n_comm_clusters * kCtaGroup);
+    if (p.comm_push)
+      comm_cta_push_loop(p, smem_ops, bar_full, cluster * kCtaGroup + static_cast<int>(cta_rank),
+                         p.n_comm_clusters * kCtaGroup);
+    else
+      comm_cta_loop(p, smem_ops, bar_full, cluster * kCtaGroup + static_cast<int>(cta_rank),
+                    p.n_comm_clusters * kCtaGroup);
   } else if (warp == 0 && lane == 0) {
     // -------------------------------------------------------- TMA producer
     const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
@@ -314,8 +409,12 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
       const TileCoord tc = tile_coord(p, t);
       if (p.mode == kModeAGBefore && tc.part != p.rank) {
-        wait_flag_ge<false>(p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk,
-                            chunk_target);
+        if (p.comm_push)   // counter bumped by the source rank's comm CTAs over NVLink
+          wait_flag_ge<true>(p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk,
+                             chunk_target);
+        else
+          wait_flag_ge<false>(p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk,
+                              chunk_target);
         fence_proxy_async();      // flag acquired by the generic proxy, data read by TMA
       }
       const int m0 = tc.m_blk * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;

@@ -31,7 +31,7 @@ class TpGemmConfig(Structure):
     _fields_ = [
         ("mode", c_int32), ("dtype", c_int32), ("b_layout", c_int32), ("cta_group", c_int32),
         ("block_n", c_int32), ("group_m", c_int32), ("num_sms", c_int32), ("n_comm_ctas", c_int32),
-        ("rank", c_int32), ("world", c_int32), ("chunk_rows", c_int32), ("reserved", c_int32),
+        ("rank", c_int32), ("world", c_int32), ("chunk_rows", c_int32), ("comm_pull", c_int32),
         ("m", c_int64), ("n", c_int64), ("k", c_int64),
         ("a", c_void_p), ("b", c_void_p),
         ("out", c_void_p * MAX_WORLD), ("peer_a", c_void_p * MAX_WORLD),

@@ -96,15 +96,19 @@ def _sync(comm) -> None:
 
 
 def _device_barrier(impl) -> None:
-    """Cross-rank sync before a timed iteration, ending with a drained device."""
+    """Cross-rank sync before a timed iteration.
+
+    With a symmetric heap the barrier is a kernel on the signal pads, enqueued on the
+    timing stream: no host synchronisation, so neither launch latency nor host-side skew
+    between the rank processes is charged to the iteration that follows. Without one
+    (CPU mode) it is the reference's dummy all-reduce + synchronize
+    (``ddlb/benchmark.py:134-137``).
+    """
     comm = impl.communicator
     if comm.world_size == 1:
-        _sync(comm)
         return
-    barrier = getattr(impl, "device_barrier", None)
-    if barrier is not None:
-        barrier()            # barrier kernel on the symmetric signal pads
-        _sync(comm)
+    if comm.is_cuda:
+        comm.symmetric_heap().barrier()
         return
     if comm.pg_initialized:
         import torch
@@ -131,6 +135,10 @@ def time_implementation(impl, num_iterations: int, backend: str, barrier: bool):
         if barrier:
             starts = [torch.cuda.Event(enable_timing=True) for _ in range(num_iterations)]
             ends = [torch.cuda.Event(enable_timing=True) for _ in range(num_iterations)]
+            if comm.world_size > 1:
+                comm.init_process_group()
+                comm.symmetric_heap()          # every implementation gets the device barrier
+            comm.barrier()
             for i in range(num_iterations):
                 _device_barrier(impl)
                 starts[i].record()

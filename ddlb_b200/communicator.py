@@ -83,10 +83,8 @@ class Communicator:
     def init_process_group(self, backend: Optional[str] = None) -> None:
         """Create the process group if none exists yet (idempotent).
 
-        Rendezvous is ``tcp://DDLB_MASTER_ADDR:port`` where the port rotates
-        with the child sequence number (see ``envs.rendezvous_port``). When
-        the default group already exists (e.g. ``bench.py`` under torchrun
-        initialised it from ``env://``) it is reused.
+        The rendezvous store is chosen by ``_rendezvous``. When the default group
+        already exists it is reused.
         """
         import torch.distributed as dist
 
@@ -101,15 +99,47 @@ class Communicator:
                     "UCC is not available in this torch build "
                     "(torch.distributed.is_ucc_available() is False)")
             backend = "ucc"
-        addr = envs.get_master_addr()
-        port = envs.rendezvous_port(self._sequence)
         kwargs: Dict[str, Any] = {}
         if backend == "nccl":
             kwargs["device_id"] = self.device
-        dist.init_process_group(backend=backend, rank=self.rank,
-                                world_size=self.world_size,
-                                init_method=f"tcp://{addr}:{port}", **kwargs)
+        store, init_method = self._rendezvous()
+        if store is not None:
+            dist.init_process_group(backend=backend, rank=self.rank, world_size=self.world_size,
+                                    store=store, **kwargs)
+        else:
+            dist.init_process_group(backend=backend, rank=self.rank, world_size=self.world_size,
+                                    init_method=init_method, **kwargs)
         self._pg_owned = True
+
+    def _rendezvous(self):
+        """``(store, init_method)`` for this child; exactly one is not None.
+
+        Collision-proof choices first (a guessed TCP port can be taken, and a rank that
+        fails to bind leaves its peers hanging in the rendezvous):
+        * one rank: an in-process ``HashStore``;
+        * in-tree launcher (``DDLB_RDZV_PREFIX``): a ``FileStore`` in a fresh directory,
+          one file per child sequence number;
+        * torchrun (agent store on ``MASTER_PORT``): a ``PrefixStore`` over a client of
+          that store, keyed by the child sequence number;
+        * otherwise (mpirun / SLURM style): ``tcp://DDLB_MASTER_ADDR:port`` with the port
+          rotating per child (the reference reuses one port, ``ddlb/envs.py:75-77``).
+        """
+        import datetime
+        import torch.distributed as dist
+        seq = self._sequence
+        if self.world_size == 1:
+            return dist.HashStore(), None
+        prefix = os.environ.get("DDLB_RDZV_PREFIX")
+        if prefix:
+            return dist.FileStore(f"{prefix}_{seq}", self.world_size), None
+        if (os.environ.get("TORCHELASTIC_USE_AGENT_STORE", "").lower() == "true"
+                and os.environ.get("MASTER_PORT") and os.environ.get("MASTER_ADDR")):
+            base = dist.TCPStore(os.environ["MASTER_ADDR"], int(os.environ["MASTER_PORT"]),
+                                 self.world_size, is_master=False,
+                                 timeout=datetime.timedelta(seconds=300))
+            run = os.environ.get("TORCHELASTIC_RUN_ID", "run")
+            return dist.PrefixStore(f"ddlb_b200/{run}/{seq}", base), None
+        return None, f"tcp://{envs.get_master_addr()}:{envs.rendezvous_port(seq)}"
 
     @property
     def pg_initialized(self) -> bool:

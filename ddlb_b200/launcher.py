@@ -29,7 +29,9 @@ def _free_port() -> int:
 
 def launch(np_: int, command: List[str], cpu: bool = False, timeout: Optional[float] = None,
            quiet_ranks: bool = True) -> int:
+    import tempfile
     port = int(os.environ.get("DDLB_MASTER_PORT", 0)) or _free_port()
+    rdzv_dir = tempfile.mkdtemp(prefix="ddlb_rdzv_")
     procs = []
     for rank in range(np_):
         env = dict(os.environ)
@@ -37,6 +39,7 @@ def launch(np_: int, command: List[str], cpu: bool = False, timeout: Optional[fl
             "RANK": str(rank), "LOCAL_RANK": str(rank), "WORLD_SIZE": str(np_),
             "LOCAL_WORLD_SIZE": str(np_), "DDLB_MASTER_ADDR": "127.0.0.1",
             "DDLB_MASTER_PORT": str(port),
+            "DDLB_RDZV_PREFIX": os.path.join(rdzv_dir, "store"),
         })
         env.pop("MASTER_PORT", None)
         if cpu:
@@ -79,6 +82,8 @@ def launch(np_: int, command: List[str], cpu: bool = False, timeout: Optional[fl
                     os.killpg(p.pid, signal.SIGKILL)
                 except ProcessLookupError:
                     pass
+    import shutil
+    shutil.rmtree(rdzv_dir, ignore_errors=True)
     return code
 
 

@@ -20,6 +20,9 @@ tile-schedule parameters of the kernel:
 ``s``              number of stages for ``coll_pipeline``.
 ``comm_sms``       CTAs used for communication (0 = auto).
 ``cta_group``      tcgen05 ``cta_group`` (0 = auto: 2 when rows/rank % 256 == 0).
+``transport``      ``push`` (default, also ``auto``/``p2p``): comm CTAs read the own shard
+                   once and post stores to every peer; ``pull``: comm CTAs read the
+                   peers' shards (one NVLink round trip per piece).
 =================  ==========================================================
 """
 from __future__ import annotations
@@ -35,7 +38,7 @@ class FusedTPColumnwise(TPColumnwise):
         "comm_sms": 0,
         "cta_group": 0,
         "block_n": 0,
-        "transport": "p2p",
+        "transport": "push",
     }
     ALLOWED_VALUES = {
         "order": ["AG_before", "AG_after"],
@@ -44,7 +47,7 @@ class FusedTPColumnwise(TPColumnwise):
         "comm_sms": (0, 64),
         "cta_group": [0, 1, 2],
         "block_n": [0, 128, 256],
-        "transport": ["auto", "p2p"],
+        "transport": ["auto", "push", "pull", "p2p"],
     }
 
     def __init__(self, *args, **kwargs):
@@ -72,7 +75,9 @@ class FusedTPColumnwise(TPColumnwise):
             heap, comm.rank, d, self.m, self.n, self.k, self.torch_dtype, self.B,
             order=self.options["order"], chunk_rows=chunk_rows,
             n_comm_ctas=int(self.options["comm_sms"]), cta_group=int(self.options["cta_group"]),
-            block_n=int(self.options["block_n"])) if d > 1 else self._single_rank_op()
+            block_n=int(self.options["block_n"]),
+            transport="pull" if self.options["transport"] == "pull" else "push",
+        ) if d > 1 else self._single_rank_op()
         self.op.a_shard.copy_(self.A)
         self.A = self.op.a_shard
         torch.cuda.synchronize()

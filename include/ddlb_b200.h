@@ -64,7 +64,7 @@ typedef struct ddlb_tp_gemm_config {
   int32_t n_comm_ctas;   /* AG_BEFORE: CTAs that pull peer shards, 0 = auto */
   int32_t rank, world;
   int32_t chunk_rows;    /* rows per pipeline chunk inside a shard, 0 = auto */
-  int32_t reserved;
+  int32_t comm_pull;     /* AG_BEFORE transport: 0 = push own shard to peers (default), 1 = pull */
   int64_t m, n, k;       /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
   /* PLAIN:     a = A[m,k]                 out[rank] = C[m,n]
    * AG_BEFORE: a = gathered A[m,k] (own shard rows already in place), peer_a[r] = rank r's
