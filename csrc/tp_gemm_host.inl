@@ -381,3 +381,105 @@ extern "C" int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, u
   }
   return 0;
 }
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant of ddlb_tp_gemm_run_emulated.
+//
+// The emulated kernel reads one parameter block per rank (tensor maps, flag and
+// buffer addresses) from global memory. ddlb_tp_gemm_run_emulated obtains that
+// scratch from cudaMallocAsync on every call. Some hosts of this library cannot do
+// that: a process that handed every remaining byte of the device to its own pool at
+// start-up (a serving engine's KV-cache arena, a framework allocator with a hard
+// cap) has nothing left for the driver to allocate from, and control loops that
+// must not block forbid calls that may take the allocator's lock or trim a pool.
+// For them the scratch lives in the array below: fixed size, part of the module
+// image, held by every device that loads the library until the process exits.
+//
+// Capacity: DDLB_EMULATED_STATIC_MAX_WORLD parameter blocks (about 1.6 KiB each).
+// ---------------------------------------------------------------------------
+namespace ddlb {
+
+static __device__ __align__(256) unsigned char
+    g_emulated_param_scratch[DDLB_EMULATED_STATIC_MAX_WORLD * sizeof(TpGemmParams)];
+
+constexpr int kMaxTrackedDevices = 64;
+// Device address of the array above, per device ordinal. In host code the symbol name
+// is only a handle: it must go through cudaGetSymbolAddress with the device current.
+static TpGemmParams* g_emulated_scratch_addr[kMaxTrackedDevices] = {};
+
+static int emulated_scratch_for_current_device(TpGemmParams** out) {
+  int dev = 0;
+  DDLB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxTrackedDevices) return set_error("device ordinal %d is not supported", dev);
+  if (g_emulated_scratch_addr[dev] == nullptr) {
+    void* addr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&addr, g_emulated_param_scratch);
+    if (e != cudaSuccess || addr == nullptr) {
+      (void)cudaGetLastError();
+      return set_error("cudaGetSymbolAddress(static scratch) on device %d: %s", dev,
+                       cudaGetErrorString(e));
+    }
+    g_emulated_scratch_addr[dev] = static_cast<TpGemmParams*>(addr);
+  }
+  *out = g_emulated_scratch_addr[dev];
+  return 0;
+}
+
+}  // namespace ddlb
+
+extern "C" int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int world,
+                                                uint32_t epoch, void* stream) {
+  using namespace ddlb;
+  if (plans == nullptr || world < 1) return set_error("bad arguments");
+  if (world > DDLB_EMULATED_STATIC_MAX_WORLD)
+    return set_error("world %d exceeds the static scratch of this entry point (%d ranks); use "
+                     "ddlb_tp_gemm_run_emulated, which allocates", world,
+                     DDLB_EMULATED_STATIC_MAX_WORLD);
+  const ddlb_tp_gemm_plan* first = plans[0];
+  for (int r = 0; r < world; ++r) {
+    if (plans[r] == nullptr) return set_error("null plan %d", r);
+    if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group)
+      return set_error("emulated ranks must use the same kernel variant");
+  }
+  int dev = 0, sms = 0;
+  DDLB_CUDA(cudaGetDevice(&dev));
+  DDLB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int g = first->res.cta_group;
+  int clusters_per_rank = (sms / world) / g;
+  const int want = first->res.grid / g;
+  if (first->cfg.num_sms > 0 && want < clusters_per_rank) clusters_per_rank = want;
+  if (clusters_per_rank <= first->params.n_comm_clusters)
+    return set_error("%d clusters per emulated rank leave none for the GEMM", clusters_per_rank);
+
+  TpGemmParams* dparams = nullptr;
+  if (int rc = emulated_scratch_for_current_device(&dparams)) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // Every block the kernel will read is rewritten here, so stale contents of earlier
+  // calls are never observed and nothing in this scratch has to start at zero.
+  for (int r = 0; r < world; ++r) {
+    plans[r]->params.epoch = epoch;
+    DDLB_CUDA(cudaMemcpyAsync(dparams + r, &plans[r]->params, sizeof(TpGemmParams),
+                              cudaMemcpyHostToDevice, st));
+  }
+  cudaLaunchConfig_t lc;
+  memset(&lc, 0, sizeof(lc));
+  lc.gridDim = dim3(static_cast<unsigned>(clusters_per_rank * g * world), 1, 1);
+  lc.blockDim = dim3(kNumThreads, 1, 1);
+  lc.dynamicSmemBytes = static_cast<size_t>(first->smem_bytes);
+  lc.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = static_cast<unsigned>(g);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  lc.attrs = attr;
+  lc.numAttrs = 1;
+  const TpGemmParams* carg = dparams;
+  void* args[2] = {&carg, &clusters_per_rank};
+  cudaError_t e = cudaLaunchKernelExC(&lc, reinterpret_cast<const void*>(first->emu_kernel), args);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    return set_error("emulated launch failed: %s", cudaGetErrorString(e));
+  }
+  return 0;
+}

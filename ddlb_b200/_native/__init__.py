@@ -77,6 +77,7 @@ def lib() -> ctypes.CDLL:
     L.ddlb_tp_gemm_info.argtypes = [c_void_p, POINTER(c_int32 * 8)]
     L.ddlb_tp_gemm_destroy.argtypes = [c_void_p]
     L.ddlb_tp_gemm_run_emulated.argtypes = [POINTER(c_void_p), c_int, c_uint32, c_void_p]
+    L.ddlb_tp_gemm_run_emulated_static.argtypes = [POINTER(c_void_p), c_int, c_uint32, c_void_p]
     L.ddlb_read_error_word.argtypes = [POINTER(c_uint32 * 4)]
     _lib = L
     return L

@@ -97,6 +97,26 @@ int ddlb_tp_gemm_destroy(ddlb_tp_gemm_plan* plan);
  * ranks that wait on each other are co-resident. No counterpart in the reference. */
 int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, uint32_t epoch, void* stream);
 
+/* Same launch as ddlb_tp_gemm_run_emulated, but it allocates nothing (this entry point has
+ * no counterpart in the reference). The per-rank parameter blocks the kernel reads, which
+ * the call above takes from cudaMallocAsync each time, sit in a fixed array inside the
+ * library image: DDLB_EMULATED_STATIC_MAX_WORLD blocks, about 13 KiB, resident on every
+ * device that loads the library until the process ends. Meant for hosts that cannot
+ * allocate device memory once they are running: processes that gave the whole device to
+ * their own arena at start-up (nothing is left for the driver's pool), and loops that
+ * must never take an allocator lock. It calls no cudaMalloc / cudaFree / pool routine.
+ *  - world > DDLB_EMULATED_STATIC_MAX_WORLD is refused with an error.
+ *  - The first call on each device looks up the array's device address (with that device
+ *    current); make that first call outside any stream capture.
+ *  - All calls share the one array. Each call rewrites every block it uses, so nothing
+ *    has to be cleared beforehand; but two calls whose work overlaps on the GPU (different
+ *    streams, same device) overwrite each other's blocks: keep calls on one stream, or
+ *    order them with events.
+ * Inputs, outputs, staging and signal words are still the caller's, through the plans. */
+#define DDLB_EMULATED_STATIC_MAX_WORLD 8
+int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int world, uint32_t epoch,
+                                     void* stream);
+
 /* device-side error word set by a kernel that timed out waiting ({code, block, aux0, aux1}) */
 int ddlb_read_error_word(uint32_t out[4]);
 
