@@ -47,6 +47,7 @@ static int make_tmap(CUtensorMap* map, void* base, int rank, const uint64_t* dim
 struct Resolved {
   int cta_group, block_n, group_m, grid, n_comm_ctas, chunk_rows;
   int tile_m, part_rows, a_rows, kk;   // kk: contraction length seen by this kernel
+  int comm_in_cta;
 };
 
 static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
@@ -108,7 +109,12 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
                        r.tile_m, r.part_rows);
     r.chunk_rows = cr;
   }
-  if (c.mode == DDLB_MODE_AG_BEFORE && c.world > 1) {
+  r.comm_in_cta = (c.mode == DDLB_MODE_AG_BEFORE && c.world > 1 && c.comm_transport == DDLB_COMM_EVERY_CTA) ? 1 : 0;
+  if (r.comm_in_cta) {
+    const int64_t chunk_bytes = static_cast<int64_t>(r.chunk_rows) * r.kk * 2;
+    if (chunk_bytes > 0xffffffffll) return set_error("chunk too large");
+  }
+  if (c.mode == DDLB_MODE_AG_BEFORE && c.world > 1 && !r.comm_in_cta) {
     int nc = c.n_comm_ctas > 0 ? c.n_comm_ctas : 16;
     nc -= nc % r.cta_group;
     if (nc < r.cta_group) nc = r.cta_group;
@@ -144,8 +150,15 @@ static int bind_kernel(ddlb_tp_gemm_plan* plan) {
   plan->kernel = reinterpret_cast<void (*)(TpGemmParams)>(k);
   auto ke = tp_gemm_emulated_kernel<G, BN, NM>;
   plan->emu_kernel = ke;
-  plan->smem_bytes = Cfg::kSmemBytes;
-  plan->stages = Cfg::kStages;
+  {
+    // operand ring depth: whatever fits beside the epilogue buffers (and the comm warp's ring)
+    const int fixed = 1024 + kEpiBytes + Cfg::kBarBytes + (plan->res.comm_in_cta ? kWarpRingBytes : 0);
+    int stages = (227 * 1024 - fixed) / Cfg::kStageBytes;
+    if (stages > Cfg::kStages) stages = Cfg::kStages;
+    if (stages < 2) return set_error("shared memory too small for the operand ring");
+    plan->stages = stages;
+    plan->smem_bytes = fixed + stages * Cfg::kStageBytes;
+  }
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(ke, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
@@ -275,7 +288,9 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   p.peer_a[c.rank] = static_cast<const uint8_t*>(c.a);
   p.chunk_bytes = static_cast<uint32_t>(static_cast<int64_t>(r.chunk_rows) * r.kk * 2);
   p.slice_bytes = r.n_comm_ctas > 0 ? p.chunk_bytes / r.n_comm_ctas : 0;
-  p.comm_push = c.comm_pull ? 0 : 1;
+  p.comm_push = c.comm_transport == DDLB_COMM_PUSH_CTAS ? 1 : 0;
+  p.comm_in_cta = r.comm_in_cta;
+  p.stages = plan->stages;
   p.stage_local = static_cast<const uint8_t*>(c.stage_local);
   p.rs_sig_off = kSigChunk;
   p.rs_tiles_per_src = (r.part_rows / kBlockM) * p.num_n_blocks;

@@ -38,6 +38,10 @@ constexpr int kSmemBudget = 193 * 1024;         // operand ring
 constexpr int kCommPiece = 16 * 1024;           // bytes per bulk copy of a comm CTA
 constexpr int kCommRing = 12;
 constexpr int kCommLag = 4;
+constexpr int kWarpPiece = 8 * 1024;         // comm warp in every CTA: piece, ring depth, store lag
+constexpr int kWarpRing = 4;
+constexpr int kWarpLag = 2;
+constexpr int kWarpRingBytes = kWarpRing * kWarpPiece;
 
 enum : int { kModePlain = 0, kModeAGBefore = 1, kModeAGAfter = 2, kModeRS = 3 };
 
@@ -70,7 +74,9 @@ struct TpGemmParams {
   uint8_t* local_a;                   // this rank's gathered-A buffer
   uint32_t chunk_bytes;               // bytes of one chunk (chunk rows * K * 2)
   uint32_t slice_bytes;               // chunk_bytes / comm CTAs
-  int comm_push;                      // 1: push own shard to peers, 0: pull peers' shards
+  int comm_push;                      // dedicated comm CTAs: 1 = push own shard, 0 = pull peers' shards
+  int comm_in_cta;                    // 1: no dedicated CTAs, warp 3 of EVERY CTA pulls pieces
+  int stages;                         // operand ring depth actually used (<= Cfg::kStages)
   // RS
   const uint8_t* stage_local;         // [2][world][part_rows][N] partials pushed by peers
   int rs_sig_off;                     // word offset of the RS counters in a signal block
@@ -334,20 +340,91 @@ __device__ __forceinline__ void comm_cta_push_loop(const TpGemmParams& p, uint8_
 }
 
 // ---------------------------------------------------------------------------
+// communication warp in EVERY CTA (AG_BEFORE, default transport). One SM sustains only
+// ~20 GB/s over NVLink whichever way the bytes move, so a handful of dedicated CTAs
+// cannot fill the links; spread over all CTAs the per-SM demand is ~5 GB/s and the
+// GEMM keeps every SM. The pieces (8 KiB) of all chunks, in arrival order, are dealt
+// round-robin to the CTAs; lane 0 of warp 3 pulls its pieces peer -> smem -> local
+// gathered buffer and bumps the chunk's counter once per piece.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void comm_warp_loop(const TpGemmParams& p, uint8_t* ring, uint32_t bar_base,
+                                               int ci, int nci) {
+  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
+  const int n_chunks = chunks_per_part * (p.world - 1);
+  const int ppc = static_cast<int>((p.chunk_bytes + kWarpPiece - 1) / kWarpPiece);   // pieces per chunk
+  const int total = n_chunks * ppc;
+  const int n_my = ci < total ? (total - ci + nci - 1) / nci : 0;
+  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
+
+  uint32_t ready_mask = 1u << p.rank;
+  auto piece_addr = [&](int i, size_t& off, uint32_t& bytes, int& part, int& cip) {
+    const int g = ci + i * nci;                    // global piece index
+    const int c = g / ppc;                         // chunk in fetch order (stage-major, peers rotated)
+    const int pc = g - c * ppc;
+    const int stage = c / (p.world - 1);
+    const int pi = c - stage * (p.world - 1);
+    int src = p.rank + 1 + pi;
+    src = src >= p.world ? src - p.world : src;
+    part = src;
+    cip = stage;
+    const uint32_t in_chunk = static_cast<uint32_t>(pc) * kWarpPiece;
+    bytes = min(static_cast<uint32_t>(kWarpPiece), p.chunk_bytes - in_chunk);
+    off = static_cast<size_t>(src) * part_bytes + static_cast<size_t>(stage) * p.chunk_bytes + in_chunk;
+  };
+  auto issue_load = [&](int i) {
+    size_t off; uint32_t bytes; int part, cip;
+    piece_addr(i, off, bytes, part, cip);
+    if (!(ready_mask & (1u << part))) {
+      wait_flag_ge<true>(p.sig_local + kSigReady + part, p.epoch);
+      ready_mask |= 1u << part;
+    }
+    const int slot = i % kWarpRing;
+    const uint32_t bar = bar_base + slot * 8;
+    mbar_arrive_expect_tx(bar, bytes);
+    bulk_load(smem_u32(ring + slot * kWarpPiece), p.peer_a[part] + off, bytes, bar);
+  };
+
+  const int prefill = n_my < kWarpRing ? n_my : kWarpRing;
+  for (int i = 0; i < prefill; ++i) issue_load(i);
+  for (int i = 0; i < n_my + kWarpLag; ++i) {
+    if (i < n_my) {
+      size_t off; uint32_t bytes; int part, cip;
+      piece_addr(i, off, bytes, part, cip);
+      const int slot = i % kWarpRing;
+      mbar_wait(bar_base + slot * 8, (i / kWarpRing) & 1);
+      bulk_store(p.local_a + off, smem_u32(ring + slot * kWarpPiece), bytes);
+    }
+    bulk_commit();
+    const int j = i - kWarpLag;
+    if (j >= 0 && j < n_my) {
+      bulk_wait<kWarpLag>();                       // piece j is in local memory
+      size_t off; uint32_t bytes; int part, cip;
+      piece_addr(j, off, bytes, part, cip);
+      fence_proxy_async();
+      red_add_release_gpu(p.sig_local + kSigChunk + part * chunks_per_part + cip, 1u);
+      if (j + kWarpRing < n_my) issue_load(j + kWarpRing);
+    }
+  }
+  bulk_wait<0>();
+}
+
+// ---------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------
 template <int kCtaGroup, int kBlockN, bool kBNMajor>
 __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cluster,
                                              const int nclusters) {
   using Cfg = TpGemmCfg<kCtaGroup, kBlockN>;
-  constexpr int kStages = Cfg::kStages;
+  const int kStages = p.stages;                               // runtime ring depth
+  const bool comm_in_cta = p.mode == kModeAGBefore && p.comm_in_cta != 0;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
   uint8_t* smem_ops = smem;                                   // [stage]{A, B}
   uint8_t* smem_epi = smem + kStages * Cfg::kStageBytes;      // [warp][2][4 KB]
-  uint8_t* smem_bar = smem_epi + kEpiBytes;
+  uint8_t* smem_comm = smem_epi + kEpiBytes;                  // comm warp ring (comm_in_cta only)
+  uint8_t* smem_bar = smem_comm + (comm_in_cta ? kWarpRingBytes : 0);
   const uint32_t bar_full = smem_u32(smem_bar);               // [kStages] (also comm ring, <= 12)
   const uint32_t bar_empty = bar_full + 12 * 8;               // [kStages]
   const uint32_t bar_tfull = bar_empty + 12 * 8;              // [2]
@@ -402,7 +479,9 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
   } else if (warp == 0 && lane == 0) {
     // -------------------------------------------------------- TMA producer
     const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
-    const uint32_t chunk_target = p.epoch * static_cast<uint32_t>(p.n_comm_clusters * kCtaGroup);
+    const uint32_t chunk_target =
+        p.epoch * (comm_in_cta ? (p.chunk_bytes + kWarpPiece - 1) / kWarpPiece
+                               : static_cast<uint32_t>(p.n_comm_clusters * kCtaGroup));
     const uint32_t full_leader = kCtaGroup == 2 ? mapa(bar_full, 0) : bar_full;
     int stage = 0;
     uint32_t phase = 0;
@@ -434,6 +513,13 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
+  } else if (warp == 3 && comm_in_cta) {
+    // -------------------------------------------------------- comm warp (every CTA)
+    const int ci = cluster * kCtaGroup + static_cast<int>(cta_rank);
+    if (ci == 0 && lane < p.world && lane != p.rank)
+      st_release_sys(p.sig_peer[lane] + kSigReady + p.rank, p.epoch);   // my shard is final
+    if (lane == 0)
+      comm_warp_loop(p, smem_comm, bar_full + 8 * 8, ci, nclusters * kCtaGroup);
   } else if (warp == 1 && lane == 0 && cta_rank == 0) {
     // -------------------------------------------------------- MMA issuer
     // K-major operand: 8-row groups 1024 B apart, k-step = 32 B inside the swizzle row.

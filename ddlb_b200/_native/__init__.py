@@ -17,6 +17,7 @@ IPC_HANDLE_BYTES = 64
 MODE_PLAIN, MODE_AG_BEFORE, MODE_AG_AFTER, MODE_RS = 0, 1, 2, 3
 DTYPE_F16, DTYPE_BF16 = 0, 1
 B_KN, B_NK = 0, 1
+COMM_EVERY_CTA, COMM_PULL_CTAS, COMM_PUSH_CTAS = 0, 1, 2
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libddlb_b200.so")
@@ -31,7 +32,7 @@ class TpGemmConfig(Structure):
     _fields_ = [
         ("mode", c_int32), ("dtype", c_int32), ("b_layout", c_int32), ("cta_group", c_int32),
         ("block_n", c_int32), ("group_m", c_int32), ("num_sms", c_int32), ("n_comm_ctas", c_int32),
-        ("rank", c_int32), ("world", c_int32), ("chunk_rows", c_int32), ("comm_pull", c_int32),
+        ("rank", c_int32), ("world", c_int32), ("chunk_rows", c_int32), ("comm_transport", c_int32),
         ("m", c_int64), ("n", c_int64), ("k", c_int64),
         ("a", c_void_p), ("b", c_void_p),
         ("out", c_void_p * MAX_WORLD), ("peer_a", c_void_p * MAX_WORLD),

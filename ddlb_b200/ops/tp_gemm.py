@@ -65,12 +65,12 @@ class TpGemmPlan:
 
 def _base_config(mode: int, dtype, m: int, n: int, k: int, rank: int, world: int,
                  b_layout: int, cta_group: int, block_n: int, group_m: int, num_sms: int,
-                 n_comm_ctas: int = 0, chunk_rows: int = 0, comm_pull: int = 0) -> N.TpGemmConfig:
+                 n_comm_ctas: int = 0, chunk_rows: int = 0, comm_transport: int = 0) -> N.TpGemmConfig:
     cfg = N.TpGemmConfig()
     cfg.mode, cfg.dtype, cfg.b_layout = mode, _dtype_code(dtype), b_layout
     cfg.cta_group, cfg.block_n, cfg.group_m, cfg.num_sms = cta_group, block_n, group_m, num_sms
     cfg.n_comm_ctas, cfg.rank, cfg.world, cfg.chunk_rows = n_comm_ctas, rank, world, chunk_rows
-    cfg.comm_pull = comm_pull
+    cfg.comm_transport = comm_transport
     cfg.m, cfg.n, cfg.k = m, n, k
     return cfg
 
@@ -140,13 +140,14 @@ class FusedAllGatherGemm(_FusedBase):
     def __init__(self, heap, rank: int, world: int, m: int, n: int, k: int, dtype, b,
                  order: str = "AG_before", chunk_rows: int = 0, n_comm_ctas: int = 0,
                  cta_group: int = 0, block_n: int = 0, group_m: int = 0, num_sms: int = 0,
-                 b_is_nk: bool = False, transport: str = "push"):
+                 b_is_nk: bool = False, transport: str = "cta"):
         super().__init__(heap, rank, world)
         import torch
         if m % world:
             raise ValueError(f"m ({m}) must be divisible by world ({world})")
-        if transport not in ("push", "pull"):
-            raise ValueError(f"transport must be 'push' or 'pull', got {transport!r}")
+        transports = {"cta": N.COMM_EVERY_CTA, "pull": N.COMM_PULL_CTAS, "push": N.COMM_PUSH_CTAS}
+        if transport not in transports:
+            raise ValueError(f"transport must be one of {sorted(transports)}, got {transport!r}")
         rows = m // world
         self.order = order
         elt = torch.empty((), dtype=dtype).element_size()
@@ -157,7 +158,7 @@ class FusedAllGatherGemm(_FusedBase):
             self.out = [torch.empty(m, n, dtype=dtype, device=b.device)]
             cfg = _base_config(N.MODE_AG_BEFORE if world > 1 else N.MODE_PLAIN, dtype, m, n, k,
                                rank, world, layout, cta_group, block_n, group_m, num_sms,
-                               n_comm_ctas, chunk_rows, 1 if transport == "pull" else 0)
+                               n_comm_ctas, chunk_rows, transports[transport])
             cfg.a = heap.ptr(a_off)
             for p in range(world):
                 cfg.peer_a[p] = heap.ptr(a_off, p)

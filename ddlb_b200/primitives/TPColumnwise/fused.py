@@ -20,9 +20,10 @@ tile-schedule parameters of the kernel:
 ``s``              number of stages for ``coll_pipeline``.
 ``comm_sms``       CTAs used for communication (0 = auto).
 ``cta_group``      tcgen05 ``cta_group`` (0 = auto: 2 when rows/rank % 256 == 0).
-``transport``      ``push`` (default, also ``auto``/``p2p``): comm CTAs read the own shard
-                   once and post stores to every peer; ``pull``: comm CTAs read the
-                   peers' shards (one NVLink round trip per piece).
+``transport``      ``cta`` (default, also ``auto``/``p2p``): a comm warp in EVERY CTA pulls
+                   8 KiB pieces of the peers' shards, so NVLink traffic is spread over all
+                   SMs and the GEMM keeps every SM. ``pull`` / ``push``: ``comm_sms``
+                   dedicated CTAs pull the peers' shards / push the own shard.
 =================  ==========================================================
 """
 from __future__ import annotations
@@ -38,7 +39,7 @@ class FusedTPColumnwise(TPColumnwise):
         "comm_sms": 0,
         "cta_group": 0,
         "block_n": 0,
-        "transport": "push",
+        "transport": "auto",
     }
     ALLOWED_VALUES = {
         "order": ["AG_before", "AG_after"],
@@ -47,7 +48,7 @@ class FusedTPColumnwise(TPColumnwise):
         "comm_sms": (0, 64),
         "cta_group": [0, 1, 2],
         "block_n": [0, 128, 256],
-        "transport": ["auto", "push", "pull", "p2p"],
+        "transport": ["auto", "cta", "push", "pull", "p2p"],
     }
 
     def __init__(self, *args, **kwargs):
@@ -76,7 +77,8 @@ class FusedTPColumnwise(TPColumnwise):
             order=self.options["order"], chunk_rows=chunk_rows,
             n_comm_ctas=int(self.options["comm_sms"]), cta_group=int(self.options["cta_group"]),
             block_n=int(self.options["block_n"]),
-            transport="pull" if self.options["transport"] == "pull" else "push",
+            transport={"auto": "cta", "p2p": "cta"}.get(self.options["transport"],
+                                                        self.options["transport"]),
         ) if d > 1 else self._single_rank_op()
         self.op.a_shard.copy_(self.A)
         self.A = self.op.a_shard

@@ -52,6 +52,9 @@ int ddlb_symm_barrier(ddlb_symm* s, void* stream);
 enum { DDLB_MODE_PLAIN = 0, DDLB_MODE_AG_BEFORE = 1, DDLB_MODE_AG_AFTER = 2, DDLB_MODE_RS = 3 };
 enum { DDLB_DTYPE_F16 = 0, DDLB_DTYPE_BF16 = 1 };
 enum { DDLB_B_ROW_MAJOR_KN = 0, DDLB_B_ROW_MAJOR_NK = 1 };
+/* who moves the peers' A shards in AG_BEFORE: a comm warp in every CTA pulling 8 KiB pieces
+ * (default), or n_comm_ctas dedicated CTAs that pull the peers' shards / push the own shard */
+enum { DDLB_COMM_EVERY_CTA = 0, DDLB_COMM_PULL_CTAS = 1, DDLB_COMM_PUSH_CTAS = 2 };
 
 typedef struct ddlb_tp_gemm_config {
   int32_t mode;          /* DDLB_MODE_* */
@@ -64,7 +67,7 @@ typedef struct ddlb_tp_gemm_config {
   int32_t n_comm_ctas;   /* AG_BEFORE: CTAs that pull peer shards, 0 = auto */
   int32_t rank, world;
   int32_t chunk_rows;    /* rows per pipeline chunk inside a shard, 0 = auto */
-  int32_t comm_pull;     /* AG_BEFORE transport: 0 = push own shard to peers (default), 1 = pull */
+  int32_t comm_transport; /* AG_BEFORE: DDLB_COMM_* */
   int64_t m, n, k;       /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
   /* PLAIN:     a = A[m,k]                 out[rank] = C[m,n]
    * AG_BEFORE: a = gathered A[m,k] (own shard rows already in place), peer_a[r] = rank r's

@@ -27,10 +27,12 @@ def _inputs(world, m, n, k, dtype, rowwise):
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-@pytest.mark.parametrize("order,chunk_rows", [("AG_before", 0), ("AG_before", 256),
-                                              ("AG_before", -1), ("AG_after", 0)])
+@pytest.mark.parametrize("order,chunk_rows,transport", [
+    ("AG_before", 0, "cta"), ("AG_before", 256, "cta"), ("AG_before", -1, "cta"),
+    ("AG_before", 0, "pull"), ("AG_before", 256, "pull"),
+    ("AG_before", 0, "push"), ("AG_before", 256, "push"), ("AG_after", 0, "cta")])
 @pytest.mark.parametrize("cta_group", [1, 2])
-def test_allgather_gemm_emulated(world, order, chunk_rows, cta_group):
+def test_allgather_gemm_emulated(world, order, chunk_rows, transport, cta_group):
     import torch
     from ddlb_b200.ops.emulation import make_emulated_heaps, run_emulated
     from ddlb_b200.ops.tp_gemm import FusedAllGatherGemm
@@ -40,7 +42,8 @@ def test_allgather_gemm_emulated(world, order, chunk_rows, cta_group):
     a, b, ref = _inputs(world, m, n, k, dtype, False)
     heaps = make_emulated_heaps(world, 2 * m * max(k, 2 * n) * 2 + (8 << 20))
     ops = [FusedAllGatherGemm(heaps[r], r, world, m, n, k, a.dtype, b, order=order,
-                              chunk_rows=cr, n_comm_ctas=2 * cta_group, cta_group=cta_group)
+                              chunk_rows=cr, n_comm_ctas=2 * cta_group, cta_group=cta_group,
+                              transport=transport)
            for r in range(world)]
     for r, op in enumerate(ops):
         op.a_shard.copy_(a[r * rows:(r + 1) * rows])
