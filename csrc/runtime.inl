@@ -197,3 +197,32 @@ extern "C" int ddlb_topology_json(char* out, int64_t cap, int64_t* needed) {
   }
   return 0;
 }
+
+// ------------------------------------------------------------------ copy diagnostic
+// Plain 128-bit load/store copy over all SMs; used by `python -m ddlb_b200.parallel.p2p_bench`
+// to measure what the NVLink path to a peer delivers (pull: src is peer memory, push: dst is).
+namespace ddlb {
+__global__ void __launch_bounds__(512) copy_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src,
+                                                   size_t n) {
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (; i + 7 * stride < n; i += 8 * stride) {
+    uint4 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = __ldcs(src + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) __stcs(dst + i + u * stride, v[u]);
+  }
+  for (; i < n; i += stride) dst[i] = src[i];
+}
+}  // namespace ddlb
+
+extern "C" int ddlb_copy(void* dst, const void* src, int64_t bytes, int blocks, void* stream) {
+  using namespace ddlb;
+  if (bytes % 16 != 0) return set_error("bytes must be a multiple of 16");
+  if (blocks <= 0) blocks = 148 * 4;
+  copy_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<uint4*>(dst), static_cast<const uint4*>(src), static_cast<size_t>(bytes / 16));
+  DDLB_CUDA(cudaGetLastError());
+  return 0;
+}

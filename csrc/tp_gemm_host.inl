@@ -109,7 +109,11 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
                        r.tile_m, r.part_rows);
     r.chunk_rows = cr;
   }
-  r.comm_in_cta = (c.mode == DDLB_MODE_AG_BEFORE && c.world > 1 && c.comm_transport == DDLB_COMM_EVERY_CTA) ? 1 : 0;
+  r.comm_in_cta = 0;
+  if (c.mode == DDLB_MODE_AG_BEFORE && c.world > 1) {
+    if (c.comm_transport == DDLB_COMM_EVERY_CTA) r.comm_in_cta = 2;       // register push, warps 2+3
+    if (c.comm_transport == DDLB_COMM_EVERY_CTA_TMA) r.comm_in_cta = 1;   // TMA pull ring, warp 3
+  }
   if (r.comm_in_cta) {
     const int64_t chunk_bytes = static_cast<int64_t>(r.chunk_rows) * r.kk * 2;
     if (chunk_bytes > 0xffffffffll) return set_error("chunk too large");
@@ -152,7 +156,7 @@ static int bind_kernel(ddlb_tp_gemm_plan* plan) {
   plan->emu_kernel = ke;
   {
     // operand ring depth: whatever fits beside the epilogue buffers (and the comm warp's ring)
-    const int fixed = 1024 + kEpiBytes + Cfg::kBarBytes + (plan->res.comm_in_cta ? kWarpRingBytes : 0);
+    const int fixed = 1024 + kEpiBytes + Cfg::kBarBytes + (plan->res.comm_in_cta == 1 ? kWarpRingBytes : 0);
     int stages = (227 * 1024 - fixed) / Cfg::kStageBytes;
     if (stages > Cfg::kStages) stages = Cfg::kStages;
     if (stages < 2) return set_error("shared memory too small for the operand ring");

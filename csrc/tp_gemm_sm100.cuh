@@ -409,6 +409,61 @@ __device__ __forceinline__ void comm_warp_loop(const TpGemmParams& p, uint8_t* r
 }
 
 // ---------------------------------------------------------------------------
+// communication warps in EVERY CTA, register path (AG_BEFORE, default transport).
+// Measured on B200/NVSwitch: a 128-bit load/store copy moves ~700 GB/s to a peer (both
+// directions busy) while cp.async.bulk through shared memory stays near 400 GB/s. So warps
+// 2 and 3 of every CTA PUSH this rank's shard: each 32 KiB unit is read once from local
+// memory into registers and stored to all d-1 peers' gathered buffers (posted writes),
+// then fenced at system scope and announced with one remote counter bump per peer. No
+// shared memory is used, all SMs keep computing, per-SM NVLink demand is ~5 GB/s.
+// ---------------------------------------------------------------------------
+constexpr int kPushUnit = 32 * 1024;
+constexpr int kPushUnroll = 8;       // 8 x 16 B per lane in flight
+
+__device__ __forceinline__ void comm_warp_push_regs(const TpGemmParams& p, int gw, int nw, int lane) {
+  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
+  const int upc = static_cast<int>((p.chunk_bytes + kPushUnit - 1) / kPushUnit);   // units per chunk
+  const int total = chunks_per_part * upc;
+  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
+
+  // a peer's gathered buffer may be overwritten once that peer has started this launch
+  if (lane < p.world && lane != p.rank) wait_flag_ge<true>(p.sig_local + kSigReady + lane, p.epoch);
+  __syncwarp();
+
+  for (int u = gw; u < total; u += nw) {
+    const int chunk = u / upc;
+    const uint32_t begin = static_cast<uint32_t>(u - chunk * upc) * kPushUnit;
+    const uint32_t end = min(begin + static_cast<uint32_t>(kPushUnit), p.chunk_bytes);
+    const size_t base = static_cast<size_t>(p.rank) * part_bytes + static_cast<size_t>(chunk) * p.chunk_bytes;
+    for (uint32_t off = begin + lane * 16; off < end; off += 32 * 16 * kPushUnroll) {
+      uint4 v[kPushUnroll];
+#pragma unroll
+      for (int i = 0; i < kPushUnroll; ++i) {
+        const uint32_t o = off + i * 512;
+        if (o < end) v[i] = __ldcs(reinterpret_cast<const uint4*>(p.local_a + base + o));
+      }
+      for (int d = 1; d < p.world; ++d) {
+        int peer = p.rank + d;
+        peer = peer >= p.world ? peer - p.world : peer;
+        uint8_t* dst = const_cast<uint8_t*>(p.peer_a[peer]) + base;
+#pragma unroll
+        for (int i = 0; i < kPushUnroll; ++i) {
+          const uint32_t o = off + i * 512;
+          if (o < end) __stcs(reinterpret_cast<uint4*>(dst + o), v[i]);
+        }
+      }
+    }
+    __threadfence_system();          // this lane's remote stores are performed
+    __syncwarp();
+    if (lane >= 1 && lane < p.world) {
+      int peer = p.rank + lane;
+      peer = peer >= p.world ? peer - p.world : peer;
+      red_add_release_sys(p.sig_peer[peer] + kSigChunk + p.rank * chunks_per_part + chunk, 1u);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------
 template <int kCtaGroup, int kBlockN, bool kBNMajor>
@@ -416,7 +471,8 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
                                              const int nclusters) {
   using Cfg = TpGemmCfg<kCtaGroup, kBlockN>;
   const int kStages = p.stages;                               // runtime ring depth
-  const bool comm_in_cta = p.mode == kModeAGBefore && p.comm_in_cta != 0;
+  const bool comm_in_cta = p.mode == kModeAGBefore && p.comm_in_cta == 1;   // TMA pull ring in warp 3
+  const bool comm_regs = p.mode == kModeAGBefore && p.comm_in_cta == 2;     // register push, warps 2+3
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -480,15 +536,16 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     // -------------------------------------------------------- TMA producer
     const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
     const uint32_t chunk_target =
-        p.epoch * (comm_in_cta ? (p.chunk_bytes + kWarpPiece - 1) / kWarpPiece
-                               : static_cast<uint32_t>(p.n_comm_clusters * kCtaGroup));
+        p.epoch * (comm_regs ? (p.chunk_bytes + kPushUnit - 1) / kPushUnit
+                   : comm_in_cta ? (p.chunk_bytes + kWarpPiece - 1) / kWarpPiece
+                                 : static_cast<uint32_t>(p.n_comm_clusters * kCtaGroup));
     const uint32_t full_leader = kCtaGroup == 2 ? mapa(bar_full, 0) : bar_full;
     int stage = 0;
     uint32_t phase = 0;
     for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
       const TileCoord tc = tile_coord(p, t);
       if (p.mode == kModeAGBefore && tc.part != p.rank) {
-        if (p.comm_push)   // counter bumped by the source rank's comm CTAs over NVLink
+        if (p.comm_push || comm_regs)   // counter bumped by the source rank over NVLink
           wait_flag_ge<true>(p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk,
                              chunk_target);
         else
@@ -513,6 +570,12 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
+  } else if ((warp == 2 || warp == 3) && comm_regs) {
+    // -------------------------------------------------------- comm warps (every CTA, registers)
+    const int ci = cluster * kCtaGroup + static_cast<int>(cta_rank);
+    if (ci == 0 && warp == 3 && lane < p.world && lane != p.rank)
+      st_release_sys(p.sig_peer[lane] + kSigReady + p.rank, p.epoch);   // my previous launch is over
+    comm_warp_push_regs(p, ci * 2 + (warp - 2), nclusters * kCtaGroup * 2, lane);
   } else if (warp == 3 && comm_in_cta) {
     // -------------------------------------------------------- comm warp (every CTA)
     const int ci = cluster * kCtaGroup + static_cast<int>(cta_rank);

@@ -17,7 +17,7 @@ IPC_HANDLE_BYTES = 64
 MODE_PLAIN, MODE_AG_BEFORE, MODE_AG_AFTER, MODE_RS = 0, 1, 2, 3
 DTYPE_F16, DTYPE_BF16 = 0, 1
 B_KN, B_NK = 0, 1
-COMM_EVERY_CTA, COMM_PULL_CTAS, COMM_PUSH_CTAS = 0, 1, 2
+COMM_EVERY_CTA, COMM_PULL_CTAS, COMM_PUSH_CTAS, COMM_EVERY_CTA_TMA = 0, 1, 2, 3
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libddlb_b200.so")
@@ -79,6 +79,7 @@ def lib() -> ctypes.CDLL:
     L.ddlb_tp_gemm_destroy.argtypes = [c_void_p]
     L.ddlb_tp_gemm_run_emulated.argtypes = [POINTER(c_void_p), c_int, c_uint32, c_void_p]
     L.ddlb_tp_gemm_run_emulated_static.argtypes = [POINTER(c_void_p), c_int, c_uint32, c_void_p]
+    L.ddlb_copy.argtypes = [c_void_p, c_void_p, c_int64, c_int, c_void_p]
     L.ddlb_read_error_word.argtypes = [POINTER(c_uint32 * 4)]
     _lib = L
     return L

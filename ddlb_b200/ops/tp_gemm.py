@@ -145,7 +145,8 @@ class FusedAllGatherGemm(_FusedBase):
         import torch
         if m % world:
             raise ValueError(f"m ({m}) must be divisible by world ({world})")
-        transports = {"cta": N.COMM_EVERY_CTA, "pull": N.COMM_PULL_CTAS, "push": N.COMM_PUSH_CTAS}
+        transports = {"cta": N.COMM_EVERY_CTA, "cta_tma": N.COMM_EVERY_CTA_TMA,
+                      "pull": N.COMM_PULL_CTAS, "push": N.COMM_PUSH_CTAS}
         if transport not in transports:
             raise ValueError(f"transport must be one of {sorted(transports)}, got {transport!r}")
         rows = m // world

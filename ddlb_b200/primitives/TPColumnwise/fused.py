@@ -20,10 +20,11 @@ tile-schedule parameters of the kernel:
 ``s``              number of stages for ``coll_pipeline``.
 ``comm_sms``       CTAs used for communication (0 = auto).
 ``cta_group``      tcgen05 ``cta_group`` (0 = auto: 2 when rows/rank % 256 == 0).
-``transport``      ``cta`` (default, also ``auto``/``p2p``): a comm warp in EVERY CTA pulls
-                   8 KiB pieces of the peers' shards, so NVLink traffic is spread over all
-                   SMs and the GEMM keeps every SM. ``pull`` / ``push``: ``comm_sms``
-                   dedicated CTAs pull the peers' shards / push the own shard.
+``transport``      ``cta`` (default, also ``auto``/``p2p``): two warps of EVERY CTA push the own
+                   shard to all peers with 128-bit loads/stores from registers, so NVLink
+                   traffic is spread over all SMs and the GEMM keeps every SM.
+                   ``cta_tma``: one warp of every CTA pulls 8 KiB pieces with bulk-async
+                   copies. ``pull`` / ``push``: ``comm_sms`` dedicated CTAs (bulk-async).
 =================  ==========================================================
 """
 from __future__ import annotations
@@ -48,7 +49,7 @@ class FusedTPColumnwise(TPColumnwise):
         "comm_sms": (0, 64),
         "cta_group": [0, 1, 2],
         "block_n": [0, 128, 256],
-        "transport": ["auto", "cta", "push", "pull", "p2p"],
+        "transport": ["auto", "cta", "cta_tma", "push", "pull", "p2p"],
     }
 
     def __init__(self, *args, **kwargs):

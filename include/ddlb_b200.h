@@ -52,9 +52,12 @@ int ddlb_symm_barrier(ddlb_symm* s, void* stream);
 enum { DDLB_MODE_PLAIN = 0, DDLB_MODE_AG_BEFORE = 1, DDLB_MODE_AG_AFTER = 2, DDLB_MODE_RS = 3 };
 enum { DDLB_DTYPE_F16 = 0, DDLB_DTYPE_BF16 = 1 };
 enum { DDLB_B_ROW_MAJOR_KN = 0, DDLB_B_ROW_MAJOR_NK = 1 };
-/* who moves the peers' A shards in AG_BEFORE: a comm warp in every CTA pulling 8 KiB pieces
- * (default), or n_comm_ctas dedicated CTAs that pull the peers' shards / push the own shard */
-enum { DDLB_COMM_EVERY_CTA = 0, DDLB_COMM_PULL_CTAS = 1, DDLB_COMM_PUSH_CTAS = 2 };
+/* who moves the A shards in AG_BEFORE. EVERY_CTA (default): two warps of every CTA push the
+ * own shard to all peers with 128-bit loads/stores from registers. EVERY_CTA_TMA: one warp
+ * of every CTA pulls 8 KiB pieces with bulk-async copies through shared memory. PULL_CTAS /
+ * PUSH_CTAS: n_comm_ctas dedicated CTAs with bulk-async copies. */
+enum { DDLB_COMM_EVERY_CTA = 0, DDLB_COMM_PULL_CTAS = 1, DDLB_COMM_PUSH_CTAS = 2,
+       DDLB_COMM_EVERY_CTA_TMA = 3 };
 
 typedef struct ddlb_tp_gemm_config {
   int32_t mode;          /* DDLB_MODE_* */
@@ -119,6 +122,10 @@ int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, uint32_t epo
 #define DDLB_EMULATED_STATIC_MAX_WORLD 8
 int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int world, uint32_t epoch,
                                      void* stream);
+
+/* Diagnostic: copy `bytes` (multiple of 16) with a 128-bit load/store kernel on `blocks` CTAs
+ * (0 = 4 per SM). With a peer-mapped src it measures pull bandwidth, with a peer-mapped dst push. */
+int ddlb_copy(void* dst, const void* src, int64_t bytes, int blocks, void* stream);
 
 /* device-side error word set by a kernel that timed out waiting ({code, block, aux0, aux1}) */
 int ddlb_read_error_word(uint32_t out[4]);
