@@ -113,6 +113,7 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
   if (c.mode == DDLB_MODE_AG_BEFORE && c.world > 1) {
     if (c.comm_transport == DDLB_COMM_EVERY_CTA) r.comm_in_cta = 2;       // register push, warps 2+3
     if (c.comm_transport == DDLB_COMM_EVERY_CTA_TMA) r.comm_in_cta = 1;   // TMA pull ring, warp 3
+    if (c.comm_transport == DDLB_COMM_EVERY_CTA_PULL) r.comm_in_cta = 3;  // register pull, warps 2+3
   }
   if (r.comm_in_cta) {
     const int64_t chunk_bytes = static_cast<int64_t>(r.chunk_rows) * r.kk * 2;

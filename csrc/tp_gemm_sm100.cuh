@@ -418,7 +418,7 @@ __device__ __forceinline__ void comm_warp_loop(const TpGemmParams& p, uint8_t* r
 // shared memory is used, all SMs keep computing, per-SM NVLink demand is ~5 GB/s.
 // ---------------------------------------------------------------------------
 constexpr int kPushUnit = 32 * 1024;
-constexpr int kPushUnroll = 8;       // 8 x 16 B per lane in flight
+constexpr int kPushUnroll = 16;      // 16 x 16 B per lane in flight: 8 KiB per warp
 
 __device__ __forceinline__ void comm_warp_push_regs(const TpGemmParams& p, int gw, int nw, int lane) {
   const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
@@ -463,6 +463,48 @@ __device__ __forceinline__ void comm_warp_push_regs(const TpGemmParams& p, int g
   }
 }
 
+// Register-path PULL counterpart of comm_warp_push_regs: the units of all peers' chunks, in
+// arrival order, are dealt round-robin to the comm warps; each is read from the peer's
+// gathered buffer into registers and stored locally, then the local chunk counter is bumped.
+__device__ __forceinline__ void comm_warp_pull_regs(const TpGemmParams& p, int gw, int nw, int lane) {
+  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
+  const int upc = static_cast<int>((p.chunk_bytes + kPushUnit - 1) / kPushUnit);
+  const int total = chunks_per_part * (p.world - 1) * upc;
+  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
+
+  if (lane < p.world && lane != p.rank) wait_flag_ge<true>(p.sig_local + kSigReady + lane, p.epoch);
+  __syncwarp();
+
+  for (int u = gw; u < total; u += nw) {
+    const int c = u / upc;                               // chunk in fetch order
+    const int stage = c / (p.world - 1);
+    const int pi = c - stage * (p.world - 1);
+    int src = p.rank + 1 + pi;
+    src = src >= p.world ? src - p.world : src;
+    const uint32_t begin = static_cast<uint32_t>(u - c * upc) * kPushUnit;
+    const uint32_t end = min(begin + static_cast<uint32_t>(kPushUnit), p.chunk_bytes);
+    const size_t base = static_cast<size_t>(src) * part_bytes + static_cast<size_t>(stage) * p.chunk_bytes;
+    const uint8_t* from = p.peer_a[src] + base;
+    for (uint32_t off = begin + lane * 16; off < end; off += 32 * 16 * kPushUnroll) {
+      uint4 v[kPushUnroll];
+#pragma unroll
+      for (int i = 0; i < kPushUnroll; ++i) {
+        const uint32_t o = off + i * 512;
+        if (o < end) v[i] = __ldcs(reinterpret_cast<const uint4*>(from + o));
+      }
+#pragma unroll
+      for (int i = 0; i < kPushUnroll; ++i) {
+        const uint32_t o = off + i * 512;
+        if (o < end) __stcg(reinterpret_cast<uint4*>(p.local_a + base + o), v[i]);
+      }
+    }
+    __threadfence();
+    __syncwarp();
+    if (lane == 0)
+      red_add_release_gpu(p.sig_local + kSigChunk + src * chunks_per_part + stage, 1u);
+  }
+}
+
 // ---------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------
@@ -472,7 +514,8 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
   using Cfg = TpGemmCfg<kCtaGroup, kBlockN>;
   const int kStages = p.stages;                               // runtime ring depth
   const bool comm_in_cta = p.mode == kModeAGBefore && p.comm_in_cta == 1;   // TMA pull ring in warp 3
-  const bool comm_regs = p.mode == kModeAGBefore && p.comm_in_cta == 2;     // register push, warps 2+3
+  const bool comm_regs = p.mode == kModeAGBefore && p.comm_in_cta >= 2;     // register path, warps 2+3
+  const bool comm_regs_pull = p.comm_in_cta == 3;
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -545,7 +588,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
       const TileCoord tc = tile_coord(p, t);
       if (p.mode == kModeAGBefore && tc.part != p.rank) {
-        if (p.comm_push || comm_regs)   // counter bumped by the source rank over NVLink
+        if (p.comm_push || (comm_regs && !comm_regs_pull))   // counter bumped over NVLink
           wait_flag_ge<true>(p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk,
                              chunk_target);
         else
@@ -575,7 +618,8 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     const int ci = cluster * kCtaGroup + static_cast<int>(cta_rank);
     if (ci == 0 && warp == 3 && lane < p.world && lane != p.rank)
       st_release_sys(p.sig_peer[lane] + kSigReady + p.rank, p.epoch);   // my previous launch is over
-    comm_warp_push_regs(p, ci * 2 + (warp - 2), nclusters * kCtaGroup * 2, lane);
+    if (comm_regs_pull) comm_warp_pull_regs(p, ci * 2 + (warp - 2), nclusters * kCtaGroup * 2, lane);
+    else comm_warp_push_regs(p, ci * 2 + (warp - 2), nclusters * kCtaGroup * 2, lane);
   } else if (warp == 3 && comm_in_cta) {
     // -------------------------------------------------------- comm warp (every CTA)
     const int ci = cluster * kCtaGroup + static_cast<int>(cta_rank);

@@ -17,7 +17,7 @@ IPC_HANDLE_BYTES = 64
 MODE_PLAIN, MODE_AG_BEFORE, MODE_AG_AFTER, MODE_RS = 0, 1, 2, 3
 DTYPE_F16, DTYPE_BF16 = 0, 1
 B_KN, B_NK = 0, 1
-COMM_EVERY_CTA, COMM_PULL_CTAS, COMM_PUSH_CTAS, COMM_EVERY_CTA_TMA = 0, 1, 2, 3
+COMM_EVERY_CTA, COMM_PULL_CTAS, COMM_PUSH_CTAS, COMM_EVERY_CTA_TMA, COMM_EVERY_CTA_PULL = 0, 1, 2, 3, 4
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libddlb_b200.so")

@@ -140,12 +140,13 @@ class FusedAllGatherGemm(_FusedBase):
     def __init__(self, heap, rank: int, world: int, m: int, n: int, k: int, dtype, b,
                  order: str = "AG_before", chunk_rows: int = 0, n_comm_ctas: int = 0,
                  cta_group: int = 0, block_n: int = 0, group_m: int = 0, num_sms: int = 0,
-                 b_is_nk: bool = False, transport: str = "cta"):
+                 b_is_nk: bool = False, transport: str = "cta_pull"):
         super().__init__(heap, rank, world)
         import torch
         if m % world:
             raise ValueError(f"m ({m}) must be divisible by world ({world})")
         transports = {"cta": N.COMM_EVERY_CTA, "cta_tma": N.COMM_EVERY_CTA_TMA,
+                      "cta_pull": N.COMM_EVERY_CTA_PULL,
                       "pull": N.COMM_PULL_CTAS, "push": N.COMM_PUSH_CTAS}
         if transport not in transports:
             raise ValueError(f"transport must be one of {sorted(transports)}, got {transport!r}")

@@ -20,11 +20,12 @@ tile-schedule parameters of the kernel:
 ``s``              number of stages for ``coll_pipeline``.
 ``comm_sms``       CTAs used for communication (0 = auto).
 ``cta_group``      tcgen05 ``cta_group`` (0 = auto: 2 when rows/rank % 256 == 0).
-``transport``      ``cta`` (default, also ``auto``/``p2p``): two warps of EVERY CTA push the own
-                   shard to all peers with 128-bit loads/stores from registers, so NVLink
+``transport``      ``cta_pull`` (default, also ``auto``/``p2p``): two warps of EVERY CTA pull the
+                   peers' shards with 128-bit loads/stores through registers, so NVLink
                    traffic is spread over all SMs and the GEMM keeps every SM.
-                   ``cta_tma``: one warp of every CTA pulls 8 KiB pieces with bulk-async
-                   copies. ``pull`` / ``push``: ``comm_sms`` dedicated CTAs (bulk-async).
+                   ``cta``: same warps, pushing the own shard to all peers. ``cta_tma``: one
+                   warp of every CTA pulls 8 KiB pieces with bulk-async copies. ``pull`` /
+                   ``push``: ``comm_sms`` dedicated CTAs (bulk-async copies).
 =================  ==========================================================
 """
 from __future__ import annotations
@@ -49,7 +50,7 @@ class FusedTPColumnwise(TPColumnwise):
         "comm_sms": (0, 64),
         "cta_group": [0, 1, 2],
         "block_n": [0, 128, 256],
-        "transport": ["auto", "cta", "cta_tma", "push", "pull", "p2p"],
+        "transport": ["auto", "cta", "cta_pull", "cta_tma", "push", "pull", "p2p"],
     }
 
     def __init__(self, *args, **kwargs):
@@ -78,7 +79,7 @@ class FusedTPColumnwise(TPColumnwise):
             order=self.options["order"], chunk_rows=chunk_rows,
             n_comm_ctas=int(self.options["comm_sms"]), cta_group=int(self.options["cta_group"]),
             block_n=int(self.options["block_n"]),
-            transport={"auto": "cta", "p2p": "cta"}.get(self.options["transport"],
+            transport={"auto": "cta_pull", "p2p": "cta_pull"}.get(self.options["transport"],
                                                         self.options["transport"]),
         ) if d > 1 else self._single_rank_op()
         self.op.a_shard.copy_(self.A)

@@ -57,7 +57,7 @@ enum { DDLB_B_ROW_MAJOR_KN = 0, DDLB_B_ROW_MAJOR_NK = 1 };
  * of every CTA pulls 8 KiB pieces with bulk-async copies through shared memory. PULL_CTAS /
  * PUSH_CTAS: n_comm_ctas dedicated CTAs with bulk-async copies. */
 enum { DDLB_COMM_EVERY_CTA = 0, DDLB_COMM_PULL_CTAS = 1, DDLB_COMM_PUSH_CTAS = 2,
-       DDLB_COMM_EVERY_CTA_TMA = 3 };
+       DDLB_COMM_EVERY_CTA_TMA = 3, DDLB_COMM_EVERY_CTA_PULL = 4 /* register path, pulling */ };
 
 typedef struct ddlb_tp_gemm_config {
   int32_t mode;          /* DDLB_MODE_* */

@@ -30,6 +30,7 @@ def _inputs(world, m, n, k, dtype, rowwise):
 @pytest.mark.parametrize("order,chunk_rows,transport", [
     ("AG_before", 0, "cta"), ("AG_before", 256, "cta"), ("AG_before", -1, "cta"),
     ("AG_before", 0, "cta_tma"), ("AG_before", 256, "cta_tma"),
+    ("AG_before", 0, "cta_pull"), ("AG_before", 256, "cta_pull"),
     ("AG_before", 0, "pull"), ("AG_before", 256, "pull"),
     ("AG_before", 0, "push"), ("AG_before", 256, "push"), ("AG_after", 0, "cta")])
 @pytest.mark.parametrize("cta_group", [1, 2])
