@@ -155,15 +155,20 @@ class FusedAllGatherGemm(_FusedBase):
         elt = torch.empty((), dtype=dtype).element_size()
         layout = N.B_NK if b_is_nk else N.B_KN
         if order == "AG_before":
-            a_off, self.a_gathered = heap.empty((m, k), dtype)
-            self.a_shard = self.a_gathered[rank * rows:(rank + 1) * rows]
             self.out = [torch.empty(m, n, dtype=dtype, device=b.device)]
             cfg = _base_config(N.MODE_AG_BEFORE if world > 1 else N.MODE_PLAIN, dtype, m, n, k,
                                rank, world, layout, cta_group, block_n, group_m, num_sms,
                                n_comm_ctas, chunk_rows, transports[transport])
-            cfg.a = heap.ptr(a_off)
-            for p in range(world):
-                cfg.peer_a[p] = heap.ptr(a_off, p)
+            if world == 1:
+                # nothing to gather: an ordinary device buffer, no symmetric heap needed
+                self.a_gathered = torch.empty(m, k, dtype=dtype, device=b.device)
+                cfg.a = self.a_gathered.data_ptr()
+            else:
+                a_off, self.a_gathered = heap.empty((m, k), dtype)
+                cfg.a = heap.ptr(a_off)
+                for p in range(world):
+                    cfg.peer_a[p] = heap.ptr(a_off, p)
+            self.a_shard = self.a_gathered[rank * rows:(rank + 1) * rows]
             cfg.out[rank] = self.out[0].data_ptr()
         elif order == "AG_after":
             self.a_shard = torch.empty(rows, k, dtype=dtype, device=b.device)
