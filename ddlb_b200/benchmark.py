@@ -89,6 +89,44 @@ def _empty_row(label, option_str, m, n, k, dtype, backend, barrier, validate, er
     return row
 
 
+class _Range:
+    """NVTX range around a benchmark phase (no-op on CPU); shows up in Nsight timelines
+    next to the ``cudaProfilerStart/Stop`` bracket. The reference emits none."""
+
+    def __init__(self, comm, name: str):
+        self._on = bool(comm.is_cuda)
+        self._name = name
+
+    def __enter__(self):
+        if self._on:
+            try:
+                import torch
+                torch.cuda.nvtx.range_push(self._name)
+            except Exception:
+                self._on = False
+        return self
+
+    def __exit__(self, *exc):
+        if self._on:
+            import torch
+            torch.cuda.nvtx.range_pop()
+
+
+class _L2Flusher:
+    """Writes a buffer larger than L2 between timed iterations (``DDLB_L2_FLUSH=1``), for
+    shapes whose working set would otherwise stay L2-resident from one run to the next."""
+
+    def __init__(self, comm):
+        self.buf = None
+        if comm.is_cuda and os.environ.get("DDLB_L2_FLUSH", "0") == "1":
+            import torch
+            self.buf = torch.empty(256 << 20, dtype=torch.uint8, device=comm.device)
+
+    def __call__(self) -> None:
+        if self.buf is not None:
+            self.buf.zero_()
+
+
 def _sync(comm) -> None:
     if comm.is_cuda:
         import torch
@@ -139,7 +177,9 @@ def time_implementation(impl, num_iterations: int, backend: str, barrier: bool):
                 comm.init_process_group()
                 comm.symmetric_heap()          # every implementation gets the device barrier
             comm.barrier()
+            flush = _L2Flusher(comm)
             for i in range(num_iterations):
+                flush()
                 _device_barrier(impl)
                 starts[i].record()
                 last = impl.run()
@@ -195,9 +235,10 @@ def _benchmark_worker_entry(impl_id: str, m: int, n: int, k: int, dtype: str,
         impl = impl_class(m=m, n=n, k=k, dtype=dtype, **options)
         comm = impl.communicator
 
-        for _ in range(num_warmups):
-            impl.run()
-        _sync(comm)
+        with _Range(comm, f"ddlb/{impl_id}/warmup"):
+            for _ in range(num_warmups):
+                impl.run()
+            _sync(comm)
 
         cudart = None
         if comm.is_cuda:
@@ -207,9 +248,10 @@ def _benchmark_worker_entry(impl_id: str, m: int, n: int, k: int, dtype: str,
                 cudart.cudaProfilerStart()
             except Exception:
                 cudart = None
-        for _ in range(PROFILED_RUNS):
-            impl.run()
-        _sync(comm)
+        with _Range(comm, f"ddlb/{impl_id}/profiled"):
+            for _ in range(PROFILED_RUNS):
+                impl.run()
+            _sync(comm)
         if cudart is not None:
             try:
                 cudart.cudaProfilerStop()
@@ -219,8 +261,9 @@ def _benchmark_worker_entry(impl_id: str, m: int, n: int, k: int, dtype: str,
         for _ in range(num_warmups):
             impl.run()
 
-        times, last_result = time_implementation(
-            impl, num_iterations, time_measurement_backend, barrier_at_each_iteration)
+        with _Range(comm, f"ddlb/{impl_id}/timed"):
+            times, last_result = time_implementation(
+                impl, num_iterations, time_measurement_backend, barrier_at_each_iteration)
         times = comm.all_reduce_max(times) if times else times
 
         row = _empty_row(label, option_str, m, n, k, dtype, time_measurement_backend,
