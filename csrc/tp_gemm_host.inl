@@ -23,9 +23,9 @@ static EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-// rank-2/3 tiled map of 16-bit elements, 128-byte swizzle
+// rank-2/3 tiled map of 16-bit (elem = 2) or 32-bit (elem = 4) elements, 128-byte swizzle
 static int make_tmap(CUtensorMap* map, void* base, int rank, const uint64_t* dims,
-                     const uint64_t* strides_bytes, const uint32_t* box) {
+                     const uint64_t* strides_bytes, const uint32_t* box, int elem = 2) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (fn == nullptr) return set_error("cuTensorMapEncodeTiled is unavailable (no CUDA driver?)");
   cuuint64_t gdims[3];
@@ -34,7 +34,8 @@ static int make_tmap(CUtensorMap* map, void* base, int rank, const uint64_t* dim
   cuuint32_t estr[3] = {1, 1, 1};
   for (int i = 0; i < rank; ++i) { gdims[i] = dims[i]; gbox[i] = box[i]; }
   for (int i = 0; i + 1 < rank; ++i) gstrides[i] = strides_bytes[i];
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_UINT16, static_cast<cuuint32_t>(rank), base, gdims,
+  CUresult r = fn(map, elem == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT16,
+                  static_cast<cuuint32_t>(rank), base, gdims,
                   gstrides, gbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS)
@@ -48,23 +49,28 @@ struct Resolved {
   int cta_group, block_n, group_m, grid, n_comm_ctas, chunk_rows;
   int tile_m, part_rows, a_rows, kk;   // kk: contraction length seen by this kernel
   int comm_in_cta;
+  int elem;   // bytes per element: 2 (fp16/bf16) or 4 (fp32 through TF32)
 };
 
 static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
   if (c.world < 1 || c.world > DDLB_MAX_WORLD || c.rank < 0 || c.rank >= c.world)
     return set_error("bad rank/world %d/%d", c.rank, c.world);
   if (c.mode < 0 || c.mode > 3) return set_error("bad mode %d", c.mode);
-  if (c.dtype != DDLB_DTYPE_F16 && c.dtype != DDLB_DTYPE_BF16) return set_error("bad dtype %d", c.dtype);
+  if (c.dtype != DDLB_DTYPE_F16 && c.dtype != DDLB_DTYPE_BF16 && c.dtype != DDLB_DTYPE_F32)
+    return set_error("bad dtype %d", c.dtype);
+  r.elem = c.dtype == DDLB_DTYPE_F32 ? 4 : 2;
+  const int row_elems = 128 / r.elem;          // elements per 128-byte swizzle row
   if (c.m <= 0 || c.n <= 0 || c.k <= 0) return set_error("bad shape");
   if (c.m % c.world != 0) return set_error("m (%lld) must be divisible by world (%d)", (long long)c.m, c.world);
   r.part_rows = static_cast<int>(c.m / c.world);
   r.kk = static_cast<int>(c.mode == DDLB_MODE_RS ? c.k / c.world : c.k);
   if (c.mode == DDLB_MODE_RS && c.k % c.world != 0)
     return set_error("k (%lld) must be divisible by world (%d)", (long long)c.k, c.world);
-  if (r.kk % 8 != 0) return set_error("contraction length %d must be a multiple of 8 (16-byte rows)", r.kk);
-  if (c.n % 8 != 0) return set_error("n must be a multiple of 8 (16-byte rows)");
-  if (c.b_layout == DDLB_B_ROW_MAJOR_KN && c.n % 64 != 0)
-    return set_error("n (%lld) must be a multiple of 64 when B is [k,n] row-major", (long long)c.n);
+  if (r.kk % (16 / r.elem) != 0)
+    return set_error("contraction length %d must be a multiple of %d (16-byte rows)", r.kk, 16 / r.elem);
+  if (c.n % (16 / r.elem) != 0) return set_error("n must be a multiple of %d (16-byte rows)", 16 / r.elem);
+  if (c.b_layout == DDLB_B_ROW_MAJOR_KN && c.n % row_elems != 0)
+    return set_error("n (%lld) must be a multiple of %d when B is [k,n] row-major", (long long)c.n, row_elems);
   r.a_rows = static_cast<int>(c.mode == DDLB_MODE_AG_AFTER ? r.part_rows : c.m);
 
   const bool sharded_rows = c.mode != DDLB_MODE_PLAIN;   // tiles must not straddle shards
@@ -97,7 +103,7 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
       // auto: about 1 MiB of A per chunk (AG) / 4 tile rows (RS), dividing the shard evenly
       const int mblks = r.part_rows / r.tile_m;
       int want = c.mode == DDLB_MODE_AG_BEFORE
-                     ? static_cast<int>((1 << 20) / (static_cast<int64_t>(r.kk) * 2 * r.tile_m))
+                     ? static_cast<int>((1 << 20) / (static_cast<int64_t>(r.kk) * r.elem * r.tile_m))
                      : mblks;
       if (want < 1) want = 1;
       if (want > mblks) want = mblks;
@@ -116,14 +122,14 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
     if (c.comm_transport == DDLB_COMM_EVERY_CTA_PULL) r.comm_in_cta = 3;  // register pull, warps 2+3
   }
   if (r.comm_in_cta) {
-    const int64_t chunk_bytes = static_cast<int64_t>(r.chunk_rows) * r.kk * 2;
+    const int64_t chunk_bytes = static_cast<int64_t>(r.chunk_rows) * r.kk * r.elem;
     if (chunk_bytes > 0xffffffffll) return set_error("chunk too large");
   }
   if (c.mode == DDLB_MODE_AG_BEFORE && c.world > 1 && !r.comm_in_cta) {
     int nc = c.n_comm_ctas > 0 ? c.n_comm_ctas : 16;
     nc -= nc % r.cta_group;
     if (nc < r.cta_group) nc = r.cta_group;
-    const int64_t chunk_bytes = static_cast<int64_t>(r.chunk_rows) * r.kk * 2;
+    const int64_t chunk_bytes = static_cast<int64_t>(r.chunk_rows) * r.kk * r.elem;
     while (nc > r.cta_group && (chunk_bytes % (static_cast<int64_t>(nc) * 16) != 0)) nc -= r.cta_group;
     if (chunk_bytes % (static_cast<int64_t>(nc) * 16) != 0)
       return set_error("chunk of %lld bytes cannot be split over %d comm CTAs", (long long)chunk_bytes, nc);
@@ -148,12 +154,12 @@ struct ddlb_tp_gemm_plan {
 
 namespace ddlb {
 
-template <int G, int BN, bool NM>
+template <int G, int BN, bool NM, bool F32 = false>
 static int bind_kernel(ddlb_tp_gemm_plan* plan) {
   using Cfg = TpGemmCfg<G, BN>;
-  auto k = tp_gemm_kernel<G, BN, NM>;
+  auto k = tp_gemm_kernel<G, BN, NM, F32>;
   plan->kernel = reinterpret_cast<void (*)(TpGemmParams)>(k);
-  auto ke = tp_gemm_emulated_kernel<G, BN, NM>;
+  auto ke = tp_gemm_emulated_kernel<G, BN, NM, F32>;
   plan->emu_kernel = ke;
   {
     // operand ring depth: whatever fits beside the epilogue buffers (and the comm warp's ring)
@@ -181,6 +187,13 @@ static int bind_kernel(ddlb_tp_gemm_plan* plan) {
 static int select_kernel(ddlb_tp_gemm_plan* plan) {
   const int g = plan->res.cta_group, bn = plan->res.block_n;
   const bool nm = plan->cfg.b_layout == DDLB_B_ROW_MAJOR_KN;
+  if (plan->res.elem == 4) {      // fp32 through kind::tf32
+    if (g == 1 && bn == 256) return nm ? bind_kernel<1, 256, true, true>(plan) : bind_kernel<1, 256, false, true>(plan);
+    if (g == 2 && bn == 256) return nm ? bind_kernel<2, 256, true, true>(plan) : bind_kernel<2, 256, false, true>(plan);
+    if (g == 1 && bn == 128) return nm ? bind_kernel<1, 128, true, true>(plan) : bind_kernel<1, 128, false, true>(plan);
+    if (g == 2 && bn == 128) return nm ? bind_kernel<2, 128, true, true>(plan) : bind_kernel<2, 128, false, true>(plan);
+    return set_error("no fp32 kernel for cta_group=%d block_n=%d", g, bn);
+  }
   if (g == 1 && bn == 256) return nm ? bind_kernel<1, 256, true>(plan) : bind_kernel<1, 256, false>(plan);
   if (g == 2 && bn == 256) return nm ? bind_kernel<2, 256, true>(plan) : bind_kernel<2, 256, false>(plan);
   if (g == 1 && bn == 128) return nm ? bind_kernel<1, 128, true>(plan) : bind_kernel<1, 128, false>(plan);
@@ -231,24 +244,26 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   memset(&p, 0, sizeof(p));
   const uint64_t N = static_cast<uint64_t>(c.n), K = static_cast<uint64_t>(r.kk);
   const int load_n = r.block_n / r.cta_group;
+  const uint64_t E = static_cast<uint64_t>(r.elem);
+  const uint32_t row_elems = static_cast<uint32_t>(128 / r.elem);   // 64 (16-bit) or 32 (fp32)
   int rc = 0;
-  {  // A: [a_rows, K] row-major, box 64 x 128
+  {  // A: [a_rows, K] row-major, box = one 128-byte row segment x 128 rows
     const uint64_t dims[2] = {K, static_cast<uint64_t>(r.a_rows)};
-    const uint64_t strides[1] = {K * 2};
-    const uint32_t box[2] = {kBlockK, kBlockM};
-    rc = make_tmap(&p.tmA, c.a, 2, dims, strides, box);
+    const uint64_t strides[1] = {K * E};
+    const uint32_t box[2] = {row_elems, kBlockM};
+    rc = make_tmap(&p.tmA, c.a, 2, dims, strides, box, r.elem);
   }
   if (rc == 0) {
-    if (c.b_layout == DDLB_B_ROW_MAJOR_KN) {  // [K, N]: 3-D view {64 n, K, N/64}
-      const uint64_t dims[3] = {64, K, N / 64};
-      const uint64_t strides[2] = {N * 2, 128};
-      const uint32_t box[3] = {64, kBlockK, static_cast<uint32_t>(load_n / 64)};
-      rc = make_tmap(&p.tmB, c.b, 3, dims, strides, box);
-    } else {                                  // [N, K]: box 64 x load_n
+    if (c.b_layout == DDLB_B_ROW_MAJOR_KN) {  // [K, N]: 3-D view {128 B of n, K, N / that}
+      const uint64_t dims[3] = {row_elems, K, N / row_elems};
+      const uint64_t strides[2] = {N * E, 128};
+      const uint32_t box[3] = {row_elems, row_elems, static_cast<uint32_t>(load_n) / row_elems};
+      rc = make_tmap(&p.tmB, c.b, 3, dims, strides, box, r.elem);
+    } else {                                  // [N, K]: box = 128 B of k x load_n rows
       const uint64_t dims[2] = {K, N};
-      const uint64_t strides[1] = {K * 2};
-      const uint32_t box[2] = {kBlockK, static_cast<uint32_t>(load_n)};
-      rc = make_tmap(&p.tmB, c.b, 2, dims, strides, box);
+      const uint64_t strides[1] = {K * E};
+      const uint32_t box[2] = {row_elems, static_cast<uint32_t>(load_n)};
+      rc = make_tmap(&p.tmB, c.b, 2, dims, strides, box, r.elem);
     }
   }
   for (int d = 0; d < c.world && rc == 0; ++d) {
@@ -258,9 +273,9 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
     else rows = static_cast<uint64_t>(c.m);
     if ((c.mode == DDLB_MODE_PLAIN || c.mode == DDLB_MODE_AG_BEFORE) && d != c.rank) continue;
     const uint64_t dims[2] = {N, rows};
-    const uint64_t strides[1] = {N * 2};
-    const uint32_t box[2] = {64, 32};
-    rc = make_tmap(&p.tmOut[d], c.out[d], 2, dims, strides, box);
+    const uint64_t strides[1] = {N * E};
+    const uint32_t box[2] = {row_elems, 32};
+    rc = make_tmap(&p.tmOut[d], c.out[d], 2, dims, strides, box, r.elem);
   }
   if (rc != 0) { delete plan; return rc; }
 
@@ -269,7 +284,7 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   p.world = c.world;
   p.num_m_blocks = (r.a_rows + r.tile_m - 1) / r.tile_m;
   p.num_n_blocks = static_cast<int>((c.n + r.block_n - 1) / r.block_n);
-  p.num_k_blocks = (r.kk + kBlockK - 1) / kBlockK;
+  p.num_k_blocks = (r.kk + static_cast<int>(row_elems) - 1) / static_cast<int>(row_elems);
   p.group_m = r.group_m;
   p.part_rows = r.part_rows;
   p.out_n = static_cast<int>(c.n);
@@ -282,7 +297,8 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   }
   p.rot0 = c.mode == DDLB_MODE_RS ? 1 : 0;
   p.n_comm_clusters = r.n_comm_ctas / r.cta_group;
-  p.idesc = make_idesc(c.dtype == DDLB_DTYPE_BF16 ? 1u : 0u, static_cast<uint32_t>(r.tile_m),
+  p.idesc = make_idesc(c.dtype == DDLB_DTYPE_F32 ? 2u : (c.dtype == DDLB_DTYPE_BF16 ? 1u : 0u),
+                       static_cast<uint32_t>(r.tile_m),
                        static_cast<uint32_t>(r.block_n), false, c.b_layout == DDLB_B_ROW_MAJOR_KN);
   p.epoch = 0;
   p.local_a = static_cast<uint8_t*>(c.a);
@@ -291,7 +307,7 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
     p.sig_peer[d] = c.sig_peer[d];
   }
   p.peer_a[c.rank] = static_cast<const uint8_t*>(c.a);
-  p.chunk_bytes = static_cast<uint32_t>(static_cast<int64_t>(r.chunk_rows) * r.kk * 2);
+  p.chunk_bytes = static_cast<uint32_t>(static_cast<int64_t>(r.chunk_rows) * r.kk * r.elem);
   p.slice_bytes = r.n_comm_ctas > 0 ? p.chunk_bytes / r.n_comm_ctas : 0;
   p.comm_push = c.comm_transport == DDLB_COMM_PUSH_CTAS ? 1 : 0;
   p.comm_in_cta = r.comm_in_cta;

@@ -508,10 +508,17 @@ __device__ __forceinline__ void comm_warp_pull_regs(const TpGemmParams& p, int g
 // ---------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------
-template <int kCtaGroup, int kBlockN, bool kBNMajor>
+// kF32: fp32 inputs and outputs through kind::tf32 (operands are read as TF32 by the tensor
+// core, fp32 accumulation). A 128-byte swizzle row then holds 32 elements and one MMA covers
+// 8 of them, so the byte geometry of the operand ring is identical to the 16-bit case.
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false>
 __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cluster,
                                              const int nclusters) {
   using Cfg = TpGemmCfg<kCtaGroup, kBlockN>;
+  constexpr int kElem = kF32 ? 4 : 2;                 // bytes per element
+  constexpr int kRowElems = 128 / kElem;              // elements per 128-byte swizzle row
+  constexpr int kKPerStage = kRowElems;               // k elements per pipeline stage
+  constexpr int kKPerMma = 32 / kElem;                // 16 (f16/bf16) or 8 (tf32)
   const int kStages = p.stages;                               // runtime ring depth
   const bool comm_in_cta = p.mode == kModeAGBefore && p.comm_in_cta == 1;   // TMA pull ring in warp 3
   const bool comm_regs = p.mode == kModeAGBefore && p.comm_in_cta >= 2;     // register path, warps 2+3
@@ -605,11 +612,11 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         if (kCtaGroup == 1 || cta_rank == 0)
           mbar_arrive_expect_tx(bar_full + stage * 8, Cfg::kStageBytes * kCtaGroup);
         const uint32_t fb = full_leader + stage * 8;
-        tma_load_2d<kCtaGroup>(smem_u32(sa), &p.tmA, fb, kb * kBlockK, m0);
+        tma_load_2d<kCtaGroup>(smem_u32(sa), &p.tmA, fb, kb * kKPerStage, m0);
         if constexpr (kBNMajor)
-          tma_load_3d<kCtaGroup>(smem_u32(sb), &p.tmB, fb, 0, kb * kBlockK, n0 / 64);
+          tma_load_3d<kCtaGroup>(smem_u32(sb), &p.tmB, fb, 0, kb * kKPerStage, n0 / kRowElems);
         else
-          tma_load_2d<kCtaGroup>(smem_u32(sb), &p.tmB, fb, kb * kBlockK, n0);
+          tma_load_2d<kCtaGroup>(smem_u32(sb), &p.tmB, fb, kb * kKPerStage, n0);
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
@@ -632,8 +639,8 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     // K-major operand: 8-row groups 1024 B apart, k-step = 32 B inside the swizzle row.
     // N-major B: 64-column blocks 8 KB apart (LBO), 8-k-row groups 1024 B apart (SBO),
     //            k-step = 16 rows * 128 B.
-    constexpr uint32_t kBLbo = kBNMajor ? 64 * kBlockK * 2 : 16;
-    constexpr uint32_t kBStep = kBNMajor ? (kUmmaK * 128) >> 4 : (kUmmaK * 2) >> 4;
+    constexpr uint32_t kBLbo = kBNMajor ? kKPerStage * 128 : 16;   // next 128-byte column block
+    constexpr uint32_t kBStep = kBNMajor ? (kKPerMma * 128) >> 4 : 32 >> 4;
     int stage = 0;
     uint32_t phase = 0;
     int acc = 0;
@@ -649,10 +656,15 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         const uint64_t adesc = make_smem_desc_sw128(sa, 16, 1024);
         const uint64_t bdesc = make_smem_desc_sw128(sa + Cfg::kStageA, kBLbo, 1024);
 #pragma unroll
-        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-          umma_f16<kCtaGroup>(tmem_d, adesc + static_cast<uint64_t>(k * ((kUmmaK * 2) >> 4)),
-                              bdesc + static_cast<uint64_t>(k * kBStep), p.idesc,
-                              static_cast<uint32_t>((kb | k) != 0));
+        for (int k = 0; k < kKPerStage / kKPerMma; ++k) {
+          if constexpr (kF32)
+            umma_tf32<kCtaGroup>(tmem_d, adesc + static_cast<uint64_t>(k * (32 >> 4)),
+                                 bdesc + static_cast<uint64_t>(k * kBStep), p.idesc,
+                                 static_cast<uint32_t>((kb | k) != 0));
+          else
+            umma_f16<kCtaGroup>(tmem_d, adesc + static_cast<uint64_t>(k * (32 >> 4)),
+                                bdesc + static_cast<uint64_t>(k * kBStep), p.idesc,
+                                static_cast<uint32_t>((kb | k) != 0));
         }
         umma_commit<kCtaGroup>(bar_empty + stage * 8);     // smem slot reusable when MMAs retire
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -707,6 +719,58 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         __syncwarp();
       }
 
+      if constexpr (kF32) {
+        // fp32 output: 32 columns (one 128-byte row segment) per step, no packing
+#pragma unroll 1
+        for (int c = 0; c < kBlockN / 32; ++c) {
+          uint32_t v[32];
+          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                                 static_cast<uint32_t>(acc * kBlockN + c * 32);
+          tmem_ld_32x32b_x32(taddr, &v[0]);
+          tmem_ld_wait();
+
+          if (rs_own) {
+            const int lr = local_row + lane;
+            for (int s = 0; s < p.world; ++s) {
+              if (s == p.rank) continue;
+              const size_t row = static_cast<size_t>(parity * p.world + s) * p.part_rows + lr;
+              const uint4* src = reinterpret_cast<const uint4*>(
+                  p.stage_local + (row * p.out_n + n0 + c * 32) * 4);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                const uint4 raw = __ldcg(src + j);
+                v[4 * j] = __float_as_uint(__uint_as_float(v[4 * j]) + __uint_as_float(raw.x));
+                v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + __uint_as_float(raw.y));
+                v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + __uint_as_float(raw.z));
+                v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + __uint_as_float(raw.w));
+              }
+            }
+          }
+
+          if (lane == 0) bulk_wait_read<1>();
+          __syncwarp();
+          const uint32_t sbase = smem_u32(ebuf + buf * kEpiBufBytes);
+          const uint32_t srow = sbase + lane * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t dst = srow + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(v[4 * j]),
+                         "r"(v[4 * j + 1]), "r"(v[4 * j + 2]), "r"(v[4 * j + 3])
+                         : "memory");
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (p.mode == kModeAGAfter) {
+              for (int d = 0; d < p.world; ++d) tma_store_2d(&p.tmOut[d], sbase, n0 + c * 32, out_row);
+            } else {
+              tma_store_2d(&p.tmOut[p.mode == kModeRS ? tc.part : p.rank], sbase, n0 + c * 32, out_row);
+            }
+            bulk_commit();
+          }
+          buf ^= 1;
+        }
+      } else {
 #pragma unroll 1
       for (int c = 0; c < kBlockN / 64; ++c) {
         uint32_t v[64];
@@ -760,6 +824,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         }
         buf ^= 1;
       }
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) {
@@ -798,25 +863,25 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
 }
 
 // One rank per process / GPU: parameters in the kernel parameter space.
-template <int kCtaGroup, int kBlockN, bool kBNMajor>
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 tp_gemm_kernel(const __grid_constant__ TpGemmParams p) {
   const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
   const int nclusters = kCtaGroup == 2 ? static_cast<int>(num_clusters_x()) : static_cast<int>(gridDim.x);
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor>(p, cluster, nclusters);
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32>(p, cluster, nclusters);
 }
 
 // Several ranks emulated by ONE launch on one GPU (tests): the grid is split into
 // `world` equal groups of clusters, group r runs rank r's parameter block. All
 // CTAs of one launch are co-resident (grid <= SM count), so ranks that wait on
 // each other make progress, which separate launches on one GPU cannot guarantee.
-template <int kCtaGroup, int kBlockN, bool kBNMajor>
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 tp_gemm_emulated_kernel(const TpGemmParams* __restrict__ plist, int clusters_per_rank) {
   const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
   const int vr = cluster / clusters_per_rank;
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor>(plist[vr], cluster - vr * clusters_per_rank,
-                                             clusters_per_rank);
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32>(plist[vr], cluster - vr * clusters_per_rank,
+                                                   clusters_per_rank);
 }
 
 }  // namespace ddlb

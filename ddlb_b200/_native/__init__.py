@@ -15,7 +15,7 @@ from typing import Optional
 MAX_WORLD = 8
 IPC_HANDLE_BYTES = 64
 MODE_PLAIN, MODE_AG_BEFORE, MODE_AG_AFTER, MODE_RS = 0, 1, 2, 3
-DTYPE_F16, DTYPE_BF16 = 0, 1
+DTYPE_F16, DTYPE_BF16, DTYPE_F32 = 0, 1, 2
 B_KN, B_NK = 0, 1
 COMM_EVERY_CTA, COMM_PULL_CTAS, COMM_PUSH_CTAS, COMM_EVERY_CTA_TMA, COMM_EVERY_CTA_PULL = 0, 1, 2, 3, 4
 

@@ -21,7 +21,19 @@ def _dtype_code(t) -> int:
         return N.DTYPE_F16
     if t == torch.bfloat16:
         return N.DTYPE_BF16
-    raise TypeError(f"the tcgen05 kind::f16 path takes float16/bfloat16, got {t}")
+    if t == torch.float32:
+        if not tf32_enabled():
+            raise TypeError(
+                "float32 runs through the kind::tf32 kernels, which have not been validated on "
+                "hardware yet; set DDLB_ENABLE_TF32=1 to use them, or use the pytorch baseline")
+        return N.DTYPE_F32
+    raise TypeError(f"the tcgen05 kernels take float16/bfloat16 (and float32 via TF32), got {t}")
+
+
+def tf32_enabled() -> bool:
+    """float32 inputs via kind::tf32 MMAs: opt-in until validated on a B200."""
+    import os
+    return os.environ.get("DDLB_ENABLE_TF32", "0") == "1"
 
 
 class TpGemmPlan:

@@ -61,14 +61,17 @@ class FusedTPColumnwise(TPColumnwise):
         comm = self.communicator
         if not comm.is_cuda:
             raise RuntimeError("the fused implementation needs a CUDA device (sm_100a)")
-        if self.torch_dtype not in (torch.float16, torch.bfloat16):
+        from ...ops.tp_gemm import tf32_enabled
+        ok_dtypes = (torch.float16, torch.bfloat16) + ((torch.float32,) if tf32_enabled() else ())
+        if self.torch_dtype not in ok_dtypes:
             raise ValueError(
-                f"fused tp_columnwise supports float16/bfloat16 (got {self.dtype}); "
+                f"fused tp_columnwise supports float16/bfloat16 (got {self.dtype}); float32 through "
+                "kind::tf32 is opt-in (DDLB_ENABLE_TF32=1) until validated on hardware; "
                 "use the pytorch baseline for other dtypes")
         d = comm.world_size
         rows = self.m // d
         chunk_rows = self._chunk_rows(rows)
-        elt = 2
+        elt = 4 if self.torch_dtype == torch.float32 else 2
         need = self.m * max(self.k, 2 * self.n) * elt + (64 << 20)
         heap = None
         if d > 1:

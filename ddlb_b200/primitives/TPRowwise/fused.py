@@ -42,9 +42,12 @@ class FusedTPRowwise(TPRowwise):
         comm = self.communicator
         if not comm.is_cuda:
             raise RuntimeError("the fused implementation needs a CUDA device (sm_100a)")
-        if self.torch_dtype not in (torch.float16, torch.bfloat16):
+        from ...ops.tp_gemm import tf32_enabled
+        ok_dtypes = (torch.float16, torch.bfloat16) + ((torch.float32,) if tf32_enabled() else ())
+        if self.torch_dtype not in ok_dtypes:
             raise ValueError(
-                f"fused tp_rowwise supports float16/bfloat16 (got {self.dtype}); "
+                f"fused tp_rowwise supports float16/bfloat16 (got {self.dtype}); float32 through "
+                "kind::tf32 is opt-in (DDLB_ENABLE_TF32=1) until validated on hardware; "
                 "use the pytorch baseline for other dtypes")
         d = comm.world_size
         rows = self.m // d
@@ -57,7 +60,7 @@ class FusedTPRowwise(TPRowwise):
         heap = None
         if d > 1:
             comm.init_process_group()
-            heap = comm.symmetric_heap(2 * self.m * self.n * 2 + (64 << 20))
+            heap = comm.symmetric_heap(2 * self.m * self.n * self.A.element_size() + (64 << 20))
         self.op = FusedGemmReduceScatter(
             heap, comm.rank, d, self.m, self.n, self.k, self.torch_dtype, self.A, self.B,
             chunk_rows=chunk_rows, cta_group=int(self.options["cta_group"]),

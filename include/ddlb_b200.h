@@ -50,7 +50,9 @@ int ddlb_symm_barrier(ddlb_symm* s, void* stream);
 
 /* --------------------------------------------------------------- fused GEMM */
 enum { DDLB_MODE_PLAIN = 0, DDLB_MODE_AG_BEFORE = 1, DDLB_MODE_AG_AFTER = 2, DDLB_MODE_RS = 3 };
-enum { DDLB_DTYPE_F16 = 0, DDLB_DTYPE_BF16 = 1 };
+/* F32: fp32 inputs and outputs computed with kind::tf32 tensor-core MMAs (fp32 accumulate);
+ * written after round 1's GPU budget was spent, not yet validated on hardware */
+enum { DDLB_DTYPE_F16 = 0, DDLB_DTYPE_BF16 = 1, DDLB_DTYPE_F32 = 2 };
 enum { DDLB_B_ROW_MAJOR_KN = 0, DDLB_B_ROW_MAJOR_NK = 1 };
 /* who moves the A shards in AG_BEFORE. EVERY_CTA (default): two warps of every CTA push the
  * own shard to all peers with 128-bit loads/stores from registers. EVERY_CTA_TMA: one warp
