@@ -34,29 +34,57 @@ def sources() -> List[str]:
     return out
 
 
+HASH_PATH = LIB_PATH + ".srchash"
+
+
+def source_hash() -> str:
+    import hashlib
+    h = hashlib.sha256()
+    for path in sources():
+        h.update(os.path.basename(path).encode())
+        with open(path, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()
+
+
 def is_stale() -> bool:
+    """True when the library is missing or was built from different sources. Compares a
+    content hash stored beside the library, not mtimes: a snapshot copy of the tree may
+    change mtimes, and a spurious rebuild in every rank of a multi-GPU run is not wanted."""
     if not os.path.exists(LIB_PATH):
         return True
-    built = os.path.getmtime(LIB_PATH)
-    return any(os.path.getmtime(s) > built for s in sources())
+    try:
+        with open(HASH_PATH) as fh:
+            return fh.read().strip() != source_hash()
+    except OSError:
+        return True
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not is_stale():
         return LIB_PATH
+    digest = source_hash()
+    tmp = f"{LIB_PATH}.{os.getpid()}.tmp"          # concurrent builders never share a file
     cmd = [nvcc_path(), *ARCH_FLAGS, "-O3", "-lineinfo", "-std=c++17", "-shared",
            "-Xcompiler", "-fPIC", "-I", INCLUDE, os.path.join(CSRC, "ddlb_b200.cu"),
-           "-o", LIB_PATH + ".tmp"]
+           "-o", tmp]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")
         print(" ".join(cmd))
     proc = subprocess.run(cmd, capture_output=True, text=True)
     if proc.returncode != 0:
+        try:
+            os.remove(tmp)
+        except OSError:
+            pass
         raise RuntimeError(f"nvcc failed ({proc.returncode}):\n{proc.stdout}\n{proc.stderr}")
     if verbose:
         print(proc.stderr)
-    os.replace(LIB_PATH + ".tmp", LIB_PATH)
+    os.replace(tmp, LIB_PATH)                      # atomic: loaders see the old or the new file
+    with open(f"{HASH_PATH}.{os.getpid()}.tmp", "w") as fh:
+        fh.write(digest + "\n")
+    os.replace(f"{HASH_PATH}.{os.getpid()}.tmp", HASH_PATH)
     return LIB_PATH
 
 
