@@ -187,6 +187,26 @@ static int bind_kernel(ddlb_tp_gemm_plan* plan) {
 static int select_kernel(ddlb_tp_gemm_plan* plan) {
   const int g = plan->res.cta_group, bn = plan->res.block_n;
   const bool nm = plan->cfg.b_layout == DDLB_B_ROW_MAJOR_KN;
+  if (plan->cfg.trace != nullptr) {
+    // traced variant exists for the flagship configuration only (16-bit, cta_group 2, BN 256)
+    if (plan->res.elem == 2 && g == 2 && bn == 256 && nm) {
+      using Cfg = TpGemmCfg<2, 256>;
+      auto k = tp_gemm_kernel<2, 256, true, false, true>;
+      plan->kernel = reinterpret_cast<void (*)(TpGemmParams)>(k);
+      plan->emu_kernel = nullptr;
+      cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+      if (e != cudaSuccess) { (void)cudaGetLastError(); return set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
+      (void)cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+      (void)cudaGetLastError();
+      const int fixed = 1024 + kEpiBytes + Cfg::kBarBytes + (plan->res.comm_in_cta == 1 ? kWarpRingBytes : 0);
+      int stages = (227 * 1024 - fixed) / Cfg::kStageBytes;
+      if (stages > Cfg::kStages) stages = Cfg::kStages;
+      plan->stages = stages;
+      plan->smem_bytes = fixed + stages * Cfg::kStageBytes;
+      return 0;
+    }
+    return set_error("tracing is compiled for fp16/bf16, cta_group=2, block_n=256, B [k,n] only");
+  }
   if (plan->res.elem == 4) {      // fp32 through kind::tf32
     if (g == 1 && bn == 256) return nm ? bind_kernel<1, 256, true, true>(plan) : bind_kernel<1, 256, false, true>(plan);
     if (g == 2 && bn == 256) return nm ? bind_kernel<2, 256, true, true>(plan) : bind_kernel<2, 256, false, true>(plan);
@@ -317,6 +337,7 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   p.rs_tiles_per_src = (r.part_rows / kBlockM) * p.num_n_blocks;
   p.sig_local = c.sig_local;
   p.sig_peer[c.rank] = c.sig_local;
+  p.trace = static_cast<uint4*>(c.trace);
   *out = plan;
   return 0;
 }
@@ -374,6 +395,7 @@ extern "C" int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, u
   const ddlb_tp_gemm_plan* first = plans[0];
   for (int r = 0; r < world; ++r) {
     if (plans[r] == nullptr) return set_error("null plan %d", r);
+    if (plans[r]->emu_kernel == nullptr) return set_error("traced plans cannot be emulated");
     if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group)
       return set_error("emulated ranks must use the same kernel variant");
   }
@@ -474,6 +496,7 @@ extern "C" int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int w
   const ddlb_tp_gemm_plan* first = plans[0];
   for (int r = 0; r < world; ++r) {
     if (plans[r] == nullptr) return set_error("null plan %d", r);
+    if (plans[r]->emu_kernel == nullptr) return set_error("traced plans cannot be emulated");
     if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group)
       return set_error("emulated ranks must use the same kernel variant");
   }

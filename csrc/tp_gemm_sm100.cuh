@@ -84,6 +84,8 @@ struct TpGemmParams {
   // signals
   uint32_t* sig_local;
   uint32_t* sig_peer[kMaxWorld];
+  // optional device trace (kTrace kernels only): [cta][role][kTraceSlots] x {tag, arg, time ns}
+  uint4* trace;
 };
 
 template <int kCtaGroup, int kBlockN>
@@ -508,10 +510,42 @@ __device__ __forceinline__ void comm_warp_pull_regs(const TpGemmParams& p, int g
 // ---------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------
+// ---------------------------------------------------------------------------
+// Opt-in device trace: a timeline of one launch without a profiler (ncu cannot replay
+// kernels that wait for other ranks). Compiled in only for kTrace instantiations, so the
+// production kernels carry no trace code at all.
+// ---------------------------------------------------------------------------
+constexpr int kTraceSlots = 128;
+constexpr int kTraceRoles = 4;   // 0 producer, 1 mma, 2 epilogue (warp 4), 3 comm (warp 2)
+enum : uint32_t {
+  kEvStart = 1, kEvTileBegin = 2, kEvFlagWaited = 3, kEvTileIssued = 4, kEvAccReady = 5,
+  kEvOwnWaited = 6, kEvTileStored = 7, kEvCommUnit = 8, kEvEnd = 9,
+};
+
+template <bool kTrace>
+struct Tracer {
+  uint4* base;
+  int n;
+  __device__ __forceinline__ Tracer(const TpGemmParams& p, int cta, int role) : base(nullptr), n(0) {
+    if constexpr (kTrace) {
+      if (p.trace != nullptr)
+        base = p.trace + (static_cast<size_t>(cta) * kTraceRoles + role) * kTraceSlots;
+    }
+  }
+  __device__ __forceinline__ void ev(uint32_t tag, uint32_t arg) {
+    if constexpr (kTrace) {
+      if (base != nullptr && n < kTraceSlots) {
+        const uint64_t t = globaltimer_ns();
+        base[n++] = make_uint4(tag, arg, static_cast<uint32_t>(t), static_cast<uint32_t>(t >> 32));
+      }
+    }
+  }
+};
+
 // kF32: fp32 inputs and outputs through kind::tf32 (operands are read as TF32 by the tensor
 // core, fp32 accumulation). A 128-byte swizzle row then holds 32 elements and one MMA covers
 // 8 of them, so the byte geometry of the operand ring is identical to the 16-bit case.
-template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false>
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kTrace = false>
 __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cluster,
                                              const int nclusters) {
   using Cfg = TpGemmCfg<kCtaGroup, kBlockN>;
@@ -592,8 +626,11 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     const uint32_t full_leader = kCtaGroup == 2 ? mapa(bar_full, 0) : bar_full;
     int stage = 0;
     uint32_t phase = 0;
+    Tracer<kTrace> tr(p, cluster * kCtaGroup + static_cast<int>(cta_rank), 0);
+    tr.ev(kEvStart, 0);
     for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
       const TileCoord tc = tile_coord(p, t);
+      tr.ev(kEvTileBegin, static_cast<uint32_t>(t));
       if (p.mode == kModeAGBefore && tc.part != p.rank) {
         if (p.comm_push || (comm_regs && !comm_regs_pull))   // counter bumped over NVLink
           wait_flag_ge<true>(p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk,
@@ -602,6 +639,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
           wait_flag_ge<false>(p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk,
                               chunk_target);
         fence_proxy_async();      // flag acquired by the generic proxy, data read by TMA
+        tr.ev(kEvFlagWaited, static_cast<uint32_t>(t));
       }
       const int m0 = tc.m_blk * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
       const int n0 = tc.n_blk * kBlockN + static_cast<int>(cta_rank) * Cfg::kLoadN;
@@ -645,6 +683,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
+    Tracer<kTrace> tr(p, cluster * kCtaGroup + static_cast<int>(cta_rank), 1);
     for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
       mbar_wait(bar_tempty + acc * 8, acc_phase ^ 1u);
       tc_fence_after();
@@ -670,6 +709,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
       umma_commit<kCtaGroup>(bar_tfull + acc * 8);         // accumulator ready for the epilogue
+      tr.ev(kEvTileIssued, static_cast<uint32_t>(t));
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
   } else if (warp >= 4) {
@@ -682,6 +722,8 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     uint32_t acc_phase = 0;
     uint32_t* pending_sig = nullptr;                        // RS: counter of the previous pushed tile
     const uint32_t parity = p.epoch & 1u;
+    Tracer<kTrace> tr(p, (warp == 4 && lane == 0) ? cluster * kCtaGroup + static_cast<int>(cta_rank) : -1, 2);
+    if (!(warp == 4 && lane == 0)) tr.base = nullptr;
     for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
       const TileCoord tc = tile_coord(p, t);
       const int row_cta = tc.m_blk * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
@@ -689,6 +731,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
       const int n0 = tc.n_blk * kBlockN;
       mbar_wait(bar_tfull + acc * 8, acc_phase);
       tc_fence_after();
+      tr.ev(kEvAccReady, static_cast<uint32_t>(t));
 
       const bool rs_push = p.mode == kModeRS && tc.part != p.rank;
       const bool rs_own = p.mode == kModeRS && tc.part == p.rank;
@@ -717,6 +760,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
           wait_flag_ge<true>(p.sig_local + p.rs_sig_off + lane * p.rs_tiles_per_src + cta_tile,
                              4u * p.epoch);
         __syncwarp();
+        tr.ev(kEvOwnWaited, static_cast<uint32_t>(t));
       }
 
       if constexpr (kF32) {
@@ -831,6 +875,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         if (kCtaGroup == 2 && cta_rank != 0) mbar_arrive_cluster(tempty_leader + acc * 8);
         else mbar_arrive(bar_tempty + acc * 8);
       }
+      tr.ev(kEvTileStored, static_cast<uint32_t>(t));
       if (rs_push)
         pending_sig = p.sig_peer[tc.part] + p.rs_sig_off + p.rank * p.rs_tiles_per_src + cta_tile;
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
@@ -842,6 +887,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         red_add_release_sys(pending_sig, 1u);
       }
     }
+    tr.ev(kEvEnd, 0);
     if (p.mode == kModeAGAfter && p.world > 1) {
       // every CTA tells every peer that its share of C has landed, then waits for
       // all CTAs of all peers so that C is complete when this kernel ends
@@ -863,12 +909,12 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
 }
 
 // One rank per process / GPU: parameters in the kernel parameter space.
-template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false>
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kTrace = false>
 __global__ void __launch_bounds__(kNumThreads, 1)
 tp_gemm_kernel(const __grid_constant__ TpGemmParams p) {
   const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
   const int nclusters = kCtaGroup == 2 ? static_cast<int>(num_clusters_x()) : static_cast<int>(gridDim.x);
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32>(p, cluster, nclusters);
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kTrace>(p, cluster, nclusters);
 }
 
 // Several ranks emulated by ONE launch on one GPU (tests): the grid is split into

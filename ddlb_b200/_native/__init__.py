@@ -13,6 +13,7 @@ from ctypes import (POINTER, Structure, byref, c_char_p, c_int, c_int32, c_int64
 from typing import Optional
 
 MAX_WORLD = 8
+TRACE_ROLES, TRACE_SLOTS = 4, 128
 IPC_HANDLE_BYTES = 64
 MODE_PLAIN, MODE_AG_BEFORE, MODE_AG_AFTER, MODE_RS = 0, 1, 2, 3
 DTYPE_F16, DTYPE_BF16, DTYPE_F32 = 0, 1, 2
@@ -38,6 +39,7 @@ class TpGemmConfig(Structure):
         ("out", c_void_p * MAX_WORLD), ("peer_a", c_void_p * MAX_WORLD),
         ("stage_local", c_void_p),
         ("sig_local", c_void_p), ("sig_peer", c_void_p * MAX_WORLD),
+        ("trace", c_void_p),
     ]
 
 

@@ -152,7 +152,7 @@ class FusedAllGatherGemm(_FusedBase):
     def __init__(self, heap, rank: int, world: int, m: int, n: int, k: int, dtype, b,
                  order: str = "AG_before", chunk_rows: int = 0, n_comm_ctas: int = 0,
                  cta_group: int = 0, block_n: int = 0, group_m: int = 0, num_sms: int = 0,
-                 b_is_nk: bool = False, transport: str = "cta_pull"):
+                 b_is_nk: bool = False, transport: str = "cta_pull", trace: bool = False):
         super().__init__(heap, rank, world)
         import torch
         if m % world:
@@ -208,8 +208,14 @@ class FusedAllGatherGemm(_FusedBase):
             raise ValueError(f"unknown order {order!r}")
         self.b = b
         cfgs = cfg if isinstance(cfg, list) else [cfg]
+        self.trace_buf = None
+        if trace:
+            from ..utils.trace import alloc_trace_buffer
+            self.trace_buf = alloc_trace_buffer(b.device)
         for c in cfgs:
             c.b = b.data_ptr()
+            if self.trace_buf is not None:
+                c.trace = self.trace_buf.data_ptr()
         if world > 1:
             self._alloc_signals(cfgs[0])
             for c in cfgs[1:]:
@@ -252,9 +258,13 @@ class FusedGemmReduceScatter(_FusedBase):
 
     def __init__(self, heap, rank: int, world: int, m: int, n: int, k: int, dtype, a, b,
                  chunk_rows: int = 0, cta_group: int = 0, block_n: int = 0, group_m: int = 0,
-                 num_sms: int = 0, b_is_nk: bool = False):
+                 num_sms: int = 0, b_is_nk: bool = False, trace: bool = False):
         super().__init__(heap, rank, world)
         import torch
+        self.trace_buf = None
+        if trace:
+            from ..utils.trace import alloc_trace_buffer
+            self.trace_buf = alloc_trace_buffer(a.device)
         if m % world or k % world:
             raise ValueError(f"m ({m}) and k ({k}) must be divisible by world ({world})")
         rows = m // world
@@ -275,6 +285,8 @@ class FusedGemmReduceScatter(_FusedBase):
             cfg.stage_local = heap.ptr(st_off)
             self._alloc_signals(cfg)
         cfg.a, cfg.b = a.data_ptr(), b.data_ptr()
+        if self.trace_buf is not None:
+            cfg.trace = self.trace_buf.data_ptr()
         self.plan = TpGemmPlan(cfg, keepalive=(a, b, self.out))
 
     def run(self, stream=None):

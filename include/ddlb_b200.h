@@ -87,7 +87,13 @@ typedef struct ddlb_tp_gemm_config {
   void* stage_local;
   uint32_t* sig_local;                  /* this op's signal words (zero-initialised) */
   uint32_t* sig_peer[DDLB_MAX_WORLD];   /* the same block on every peer */
+  /* optional device trace buffer (NULL = off): grid * DDLB_TRACE_ROLES * DDLB_TRACE_SLOTS
+   * records of 16 bytes {tag, arg, time_lo, time_hi (globaltimer ns)}, zero-initialised by the
+   * caller. Only for fp16/bf16, cta_group 2, block_n 256, B [k,n]. No reference counterpart. */
+  void* trace;
 } ddlb_tp_gemm_config;
+#define DDLB_TRACE_ROLES 4
+#define DDLB_TRACE_SLOTS 128
 
 typedef struct ddlb_tp_gemm_plan ddlb_tp_gemm_plan;
 
