@@ -7,8 +7,8 @@ echo "=== pytest multigpu"; timeout 600 python -m pytest tests/test_multigpu.py 
 echo "=== bench ours N=$N"; timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 100 --warmup 10 2>gpurun_out/bench_ours_$N.err | tee gpurun_out/bench_ours_n$N.json | cut -c1-600; tail -3 gpurun_out/bench_ours_$N.err
 echo "=== bench reference N=$N"; timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29521 bench.py --impl reference --gpus $N --steps 30 --warmup 5 2>gpurun_out/bench_ref_$N.err | tee gpurun_out/bench_ref_n$N.json | cut -c1-600; tail -3 gpurun_out/bench_ref_$N.err
 echo "=== harness sweeps"
-timeout 900 python -m ddlb_b200.launcher -np $N --timeout 800 scripts/run_benchmark.py scripts/dev_perf8_col.json 2>&1 | grep -E "Error|error|Traceback" | head -5
-timeout 600 python -m ddlb_b200.launcher -np $N --timeout 500 scripts/run_benchmark.py scripts/dev_perf8_row.json 2>&1 | grep -E "Error|error|Traceback" | head -5
+timeout 900 python -m ddlb_b200.launcher -np $N --timeout 800 scripts/run_benchmark.py scripts/dev/dev_perf8_col.json 2>&1 | grep -E "Error|error|Traceback" | head -5
+timeout 600 python -m ddlb_b200.launcher -np $N --timeout 500 scripts/run_benchmark.py scripts/dev/dev_perf8_row.json 2>&1 | grep -E "Error|error|Traceback" | head -5
 python - <<'PY'
 import pandas as pd, glob
 pd.set_option("display.width", 250); pd.set_option("display.max_colwidth", 100)

@@ -2,8 +2,8 @@
 N=${1:-2}
 mkdir -p gpurun_out results
 {
-timeout 900 python -m ddlb_b200.launcher -np $N --timeout 800 scripts/run_benchmark.py scripts/dev_perf_col.json 2>&1 | grep -E "Error|error|Traceback" | head
-timeout 600 python -m ddlb_b200.launcher -np $N --timeout 500 scripts/run_benchmark.py scripts/dev_perf_row.json 2>&1 | grep -E "Error|error|Traceback" | head
+timeout 900 python -m ddlb_b200.launcher -np $N --timeout 800 scripts/run_benchmark.py scripts/dev/dev_perf_col.json 2>&1 | grep -E "Error|error|Traceback" | head
+timeout 600 python -m ddlb_b200.launcher -np $N --timeout 500 scripts/run_benchmark.py scripts/dev/dev_perf_row.json 2>&1 | grep -E "Error|error|Traceback" | head
 python - <<'PY'
 import pandas as pd, glob
 pd.set_option("display.width", 250); pd.set_option("display.max_colwidth", 90)
