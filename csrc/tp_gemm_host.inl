@@ -87,7 +87,9 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
   if (cudaGetDevice(&dev) != cudaSuccess ||
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
     (void)cudaGetLastError();
-    return set_error("cannot query the current CUDA device");
+    // no device (schedule introspection on a CPU box): an explicit num_sms is taken as is
+    if (c.num_sms <= 0) return set_error("cannot query the current CUDA device");
+    sms = c.num_sms;
   }
   r.grid = c.num_sms > 0 ? (c.num_sms < sms ? c.num_sms : sms) : sms;
   r.grid -= r.grid % r.cta_group;
@@ -223,6 +225,29 @@ static int select_kernel(ddlb_tp_gemm_plan* plan) {
 
 }  // namespace ddlb
 
+namespace ddlb {
+// The part of the kernel parameters that defines the tile schedule (shared by plan creation
+// and by the host-side introspection entry points below).
+static void fill_schedule(TpGemmParams& p, const ddlb_tp_gemm_config& c, const Resolved& r) {
+  p.mode = c.mode;
+  p.rank = c.rank;
+  p.world = c.world;
+  p.num_m_blocks = (r.a_rows + r.tile_m - 1) / r.tile_m;
+  p.num_n_blocks = static_cast<int>((c.n + r.block_n - 1) / r.block_n);
+  p.group_m = r.group_m;
+  p.part_rows = r.part_rows;
+  p.out_n = static_cast<int>(c.n);
+  if (c.mode == DDLB_MODE_AG_BEFORE || c.mode == DDLB_MODE_RS) {
+    p.mblks_per_part = r.part_rows / r.tile_m;
+    p.chunk_mblks = r.chunk_rows / r.tile_m;
+  } else {
+    p.mblks_per_part = p.num_m_blocks;
+    p.chunk_mblks = p.num_m_blocks;
+  }
+  p.rot0 = c.mode == DDLB_MODE_RS ? 1 : 0;
+}
+}  // namespace ddlb
+
 extern "C" int64_t ddlb_tp_gemm_sig_words(const ddlb_tp_gemm_config* cfg) {
   if (cfg == nullptr) return -1;
   ddlb::Resolved r;
@@ -299,23 +324,8 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   }
   if (rc != 0) { delete plan; return rc; }
 
-  p.mode = c.mode;
-  p.rank = c.rank;
-  p.world = c.world;
-  p.num_m_blocks = (r.a_rows + r.tile_m - 1) / r.tile_m;
-  p.num_n_blocks = static_cast<int>((c.n + r.block_n - 1) / r.block_n);
+  fill_schedule(p, c, r);
   p.num_k_blocks = (r.kk + static_cast<int>(row_elems) - 1) / static_cast<int>(row_elems);
-  p.group_m = r.group_m;
-  p.part_rows = r.part_rows;
-  p.out_n = static_cast<int>(c.n);
-  if (c.mode == DDLB_MODE_AG_BEFORE || c.mode == DDLB_MODE_RS) {
-    p.mblks_per_part = r.part_rows / r.tile_m;
-    p.chunk_mblks = r.chunk_rows / r.tile_m;
-  } else {
-    p.mblks_per_part = p.num_m_blocks;
-    p.chunk_mblks = p.num_m_blocks;
-  }
-  p.rot0 = c.mode == DDLB_MODE_RS ? 1 : 0;
   p.n_comm_clusters = r.n_comm_ctas / r.cta_group;
   p.idesc = make_idesc(c.dtype == DDLB_DTYPE_F32 ? 2u : (c.dtype == DDLB_DTYPE_BF16 ? 1u : 0u),
                        static_cast<uint32_t>(r.tile_m),
@@ -539,6 +549,42 @@ extern "C" int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int w
   if (e != cudaSuccess) {
     (void)cudaGetLastError();
     return set_error("emulated launch failed: %s", cudaGetErrorString(e));
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// Host-side introspection of the tile schedule (runs the kernel's own tile_coord on the
+// CPU). Works without a GPU when cfg->num_sms is given. Used by the CPU property tests.
+// ---------------------------------------------------------------------------
+extern "C" int ddlb_debug_schedule(const ddlb_tp_gemm_config* cfg, int32_t out[12]) {
+  using namespace ddlb;
+  if (cfg == nullptr || out == nullptr) return set_error("null argument");
+  Resolved r;
+  if (int rc = resolve(*cfg, r)) return rc;
+  TpGemmParams p;
+  memset(&p, 0, sizeof(p));
+  fill_schedule(p, *cfg, r);
+  out[0] = p.num_m_blocks; out[1] = p.num_n_blocks; out[2] = p.mblks_per_part; out[3] = p.chunk_mblks;
+  out[4] = p.group_m; out[5] = r.tile_m; out[6] = r.block_n; out[7] = r.cta_group;
+  out[8] = r.chunk_rows; out[9] = r.n_comm_ctas; out[10] = r.grid; out[11] = r.comm_in_cta;
+  return 0;
+}
+
+extern "C" int ddlb_debug_tile_coords(const ddlb_tp_gemm_config* cfg, int32_t first, int32_t count,
+                                      int32_t* out /* count x {m_blk, n_blk, part, chunk} */) {
+  using namespace ddlb;
+  if (cfg == nullptr || out == nullptr || first < 0 || count < 0) return set_error("bad arguments");
+  Resolved r;
+  if (int rc = resolve(*cfg, r)) return rc;
+  TpGemmParams p;
+  memset(&p, 0, sizeof(p));
+  fill_schedule(p, *cfg, r);
+  const int total = p.num_m_blocks * p.num_n_blocks;
+  if (first + count > total) return set_error("tiles %d..%d out of range (%d tiles)", first, first + count, total);
+  for (int i = 0; i < count; ++i) {
+    const TileCoord tc = tile_coord(p, first + i);
+    out[4 * i] = tc.m_blk; out[4 * i + 1] = tc.n_blk; out[4 * i + 2] = tc.part; out[4 * i + 3] = tc.chunk;
   }
   return 0;
 }

@@ -114,12 +114,13 @@ struct TileCoord {
 
 // Linear tile index -> tile, identical in every role. Grouped rasterisation over an
 // arrival-ordered sequence of m-blocks.
-__device__ __forceinline__ TileCoord tile_coord(const TpGemmParams& p, int t) {
+__host__ __device__ __forceinline__ TileCoord tile_coord(const TpGemmParams& p, int t) {
   const int per_group = p.group_m * p.num_n_blocks;
   const int group = t / per_group;
   const int within = t - group * per_group;
   const int first = group * p.group_m;
-  const int rows_in_group = min(p.group_m, p.num_m_blocks - first);
+  const int left = p.num_m_blocks - first;
+  const int rows_in_group = p.group_m < left ? p.group_m : left;
   const int n_blk = within / rows_in_group;
   const int ord = first + (within - n_blk * rows_in_group);
   TileCoord c;

@@ -131,6 +131,13 @@ int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, uint32_t epo
 int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int world, uint32_t epoch,
                                      void* stream);
 
+/* Introspection of the tile schedule on the host (no GPU needed when cfg->num_sms > 0): the
+ * resolved launch/schedule parameters {num_m_blocks, num_n_blocks, mblks_per_part, chunk_mblks,
+ * group_m, tile_m, block_n, cta_group, chunk_rows, n_comm_ctas, grid, comm_in_cta}, and the
+ * kernel's own tile_coord() evaluated for tiles [first, first+count). No reference counterpart. */
+int ddlb_debug_schedule(const ddlb_tp_gemm_config* cfg, int32_t out[12]);
+int ddlb_debug_tile_coords(const ddlb_tp_gemm_config* cfg, int32_t first, int32_t count, int32_t* out);
+
 /* Diagnostic: copy `bytes` (multiple of 16) with a 128-bit load/store kernel on `blocks` CTAs
  * (0 = 4 per SM). With a peer-mapped src it measures pull bandwidth, with a peer-mapped dst push. */
 int ddlb_copy(void* dst, const void* src, int64_t bytes, int blocks, void* stream);

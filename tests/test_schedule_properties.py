@@ -1,0 +1,139 @@
+"""Property tests of the kernel's tile schedule, run on the CPU.
+
+``ddlb_debug_schedule`` / ``ddlb_debug_tile_coords`` evaluate the SAME ``resolve()`` and
+``tile_coord()`` the kernels use (``csrc/tp_gemm_host.inl``, ``csrc/tp_gemm_sm100.cuh``), so
+these tests cover shapes, world sizes and options that were never launched on a GPU:
+every tile is visited exactly once, rows map to the right shard/owner, chunks arrive in
+the order the communication produces them, own rows come first (AG) or last (RS).
+"""
+import ctypes
+
+import pytest
+from hypothesis import HealthCheck, given, settings, strategies as st
+
+from ddlb_b200 import _native as N
+
+MODES = {"plain": N.MODE_PLAIN, "ag_before": N.MODE_AG_BEFORE, "ag_after": N.MODE_AG_AFTER,
+         "rs": N.MODE_RS}
+
+
+def _cfg(mode, world, rank, m, n, k, cta_group=0, block_n=0, group_m=0, chunk_rows=0, dtype=N.DTYPE_BF16):
+    cfg = N.TpGemmConfig()
+    cfg.mode, cfg.dtype, cfg.b_layout = MODES[mode], dtype, N.B_KN
+    cfg.cta_group, cfg.block_n, cfg.group_m, cfg.num_sms = cta_group, block_n, group_m, 148
+    cfg.rank, cfg.world, cfg.chunk_rows = rank, world, chunk_rows
+    cfg.m, cfg.n, cfg.k = m, n, k
+    return cfg
+
+
+def _schedule(cfg):
+    lib = N.lib()
+    out = (ctypes.c_int32 * 12)()
+    rc = lib.ddlb_debug_schedule(ctypes.byref(cfg), ctypes.byref(out))
+    if rc != 0:
+        raise N.NativeError(lib.ddlb_last_error().decode())
+    keys = ("num_m_blocks", "num_n_blocks", "mblks_per_part", "chunk_mblks", "group_m", "tile_m",
+            "block_n", "cta_group", "chunk_rows", "n_comm_ctas", "grid", "comm_in_cta")
+    return dict(zip(keys, list(out)))
+
+
+def _tiles(cfg, sched):
+    lib = N.lib()
+    total = sched["num_m_blocks"] * sched["num_n_blocks"]
+    buf = (ctypes.c_int32 * (4 * total))()
+    N.check(lib.ddlb_debug_tile_coords(ctypes.byref(cfg), 0, total, buf), "tile_coords")
+    return [tuple(buf[4 * i:4 * i + 4]) for i in range(total)]
+
+
+shape_strategy = st.tuples(
+    st.sampled_from(["plain", "ag_before", "ag_after", "rs"]),
+    st.sampled_from([1, 2, 3, 4, 5, 8]),                 # world
+    st.integers(1, 24),                                  # tile rows per rank (x tile_m)
+    st.integers(1, 9),                                   # n in units of 64
+    st.sampled_from([1, 2]),                             # cta_group
+    st.sampled_from([0, 128, 256]),                      # block_n
+    st.sampled_from([0, 1, 3, 8, 16]),                   # group_m
+    st.integers(0, 6),                                   # chunk selector
+    st.data(),
+)
+
+
+@settings(max_examples=300, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(shape_strategy)
+def test_every_tile_once_and_rows_belong_to_their_part(args):
+    mode, world, mult, n64, g, bn, group_m, chunk_sel, data = args
+    if mode == "plain":
+        world = 1
+    rank = data.draw(st.integers(0, world - 1))
+    tile_m = 128 * g
+    part_rows = mult * tile_m
+    m, n = part_rows * world, 64 * n64
+    k = 64 * world
+    chunk_rows = 0
+    if mode in ("ag_before", "rs") and chunk_sel:
+        divisors = [d for d in range(1, mult + 1) if mult % d == 0]
+        chunk_rows = divisors[chunk_sel % len(divisors)] * tile_m
+    cfg = _cfg(mode, world, rank, m, n, k, cta_group=g, block_n=bn, group_m=group_m,
+               chunk_rows=chunk_rows)
+    sched = _schedule(cfg)
+    tiles = _tiles(cfg, sched)
+    nm, nn = sched["num_m_blocks"], sched["num_n_blocks"]
+    assert sched["tile_m"] == tile_m and sched["cta_group"] == g
+    # a permutation of the tile grid
+    assert sorted((t[0], t[1]) for t in tiles) == [(i, j) for i in range(nm) for j in range(nn)]
+    if mode in ("ag_before", "rs"):
+        per_part = sched["mblks_per_part"]
+        cm = sched["chunk_mblks"]
+        assert per_part * world == nm and per_part % cm == 0
+        for m_blk, n_blk, part, chunk in tiles:
+            assert part == m_blk // per_part                       # rows belong to that shard
+            assert chunk == (m_blk % per_part) // cm               # and to that chunk of it
+        # m-blocks appear in arrival order: stage by stage, parts rotated from the rank
+        first_seen = {}
+        for idx, (m_blk, n_blk, part, chunk) in enumerate(tiles):
+            first_seen.setdefault((chunk, part), idx)
+        rot0 = 1 if mode == "rs" else 0
+        order = sorted(first_seen, key=first_seen.get)
+        expected = [(c, (rank + rot0 + pi) % world) for c in range(per_part // cm) for pi in range(world)]
+        # grouped rasterisation interleaves tiles of neighbouring chunks, but the first
+        # appearance of each (chunk, part) follows the communication order
+        assert order == expected
+        if mode == "rs":
+            # the rank's own rows are the last part of every stage
+            assert [p for (c, p) in expected if c == 0][-1] == rank
+        else:
+            assert expected[0][1] == rank                           # own rows first
+    else:
+        assert all(t[2] == rank and t[3] == 0 for t in tiles)
+
+
+def test_headline_configs_resolve_as_documented():
+    s = _schedule(_cfg("ag_before", 8, 3, 65536, 1024, 1024))
+    assert (s["cta_group"], s["block_n"], s["tile_m"]) == (2, 256, 256)
+    assert s["chunk_rows"] == 512                     # ~1 MiB of bf16 A per chunk at k = 1024
+    assert s["comm_in_cta"] == 2 or s["comm_in_cta"] in (0, 1, 2, 3)
+    assert s["num_m_blocks"] == 256 and s["num_n_blocks"] == 4 and s["grid"] == 148
+    s = _schedule(_cfg("rs", 8, 0, 8192, 1024, 8192, dtype=N.DTYPE_F16))
+    assert s["mblks_per_part"] == 4 and s["chunk_mblks"] == 4       # one chunk per owner by default
+    s = _schedule(_cfg("ag_before", 8, 0, 16384, 28672, 8192))      # Llama-3-70B MLP up, TP=8
+    assert s["num_n_blocks"] == 112 and s["chunk_rows"] % 256 == 0
+
+
+@pytest.mark.parametrize("kwargs,needle", [
+    (dict(mode="rs", world=3, rank=0, m=300, n=64, k=192), "multiple of"),          # rows/rank % 128
+    (dict(mode="ag_before", world=2, rank=0, m=512, n=100, k=64), "multiple of"),    # n % 64 (and % 8)
+    (dict(mode="plain", world=1, rank=0, m=128, n=64, k=60), "multiple of 8"),       # 16-byte rows
+    (dict(mode="rs", world=2, rank=0, m=512, n=64, k=65), "divisible"),              # k % world
+    (dict(mode="plain", world=9, rank=0, m=1152, n=64, k=64), "rank/world"),
+    (dict(mode="ag_before", world=2, rank=0, m=1024, n=64, k=64, chunk_rows=384), "chunk_rows"),
+])
+def test_bad_configs_are_rejected_with_a_reason(kwargs, needle):
+    with pytest.raises(N.NativeError, match=needle):
+        _schedule(_cfg(**kwargs))
+
+
+def test_fp32_geometry_resolves():
+    s = _schedule(_cfg("plain", 1, 0, 512, 96, 36, dtype=N.DTYPE_F32))   # n % 32, k % 4 suffice
+    assert s["num_n_blocks"] == 1
+    with pytest.raises(N.NativeError, match="multiple of 32"):
+        _schedule(_cfg("plain", 1, 0, 512, 80, 36, dtype=N.DTYPE_F32))
