@@ -588,3 +588,31 @@ extern "C" int ddlb_debug_tile_coords(const ddlb_tp_gemm_config* cfg, int32_t fi
   }
   return 0;
 }
+
+// All units the register-path comm warps of `cfg->rank` process in AG_BEFORE (pull transport),
+// produced by the kernel's own pull_unit(): out = count x {src, chunk, begin, end, base}.
+extern "C" int ddlb_debug_pull_units(const ddlb_tp_gemm_config* cfg, int64_t cap, int64_t* out,
+                                     int64_t* count) {
+  using namespace ddlb;
+  if (cfg == nullptr || count == nullptr) return set_error("null argument");
+  if (cfg->mode != DDLB_MODE_AG_BEFORE || cfg->world < 2) return set_error("AG_BEFORE with world >= 2 only");
+  Resolved r;
+  if (int rc = resolve(*cfg, r)) return rc;
+  TpGemmParams p;
+  memset(&p, 0, sizeof(p));
+  fill_schedule(p, *cfg, r);
+  p.chunk_bytes = static_cast<uint32_t>(static_cast<int64_t>(r.chunk_rows) * r.kk * r.elem);
+  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
+  const int upc = static_cast<int>((p.chunk_bytes + kPushUnit - 1) / kPushUnit);
+  const int64_t total = static_cast<int64_t>(chunks_per_part) * (p.world - 1) * upc;
+  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
+  *count = total;
+  if (out == nullptr) return 0;
+  if (cap < total) return set_error("buffer holds %lld units, %lld needed", (long long)cap, (long long)total);
+  for (int64_t u = 0; u < total; ++u) {
+    const CommUnit cu = pull_unit(p, static_cast<int>(u), upc, part_bytes);
+    out[5 * u] = cu.src; out[5 * u + 1] = cu.chunk; out[5 * u + 2] = cu.begin; out[5 * u + 3] = cu.end;
+    out[5 * u + 4] = static_cast<int64_t>(cu.base);
+  }
+  return 0;
+}

@@ -466,6 +466,33 @@ __device__ __forceinline__ void comm_warp_push_regs(const TpGemmParams& p, int g
   }
 }
 
+// One unit of work of a register-path comm warp: `kPushUnit` bytes [begin, end) of chunk
+// `chunk` of rank `src`'s shard; `base` is the byte offset of that chunk in a gathered buffer.
+// Host-callable so the CPU tests can check that the units tile the shards exactly.
+struct CommUnit {
+  int src;
+  int chunk;
+  uint32_t begin, end;
+  size_t base;
+};
+
+__host__ __device__ __forceinline__ CommUnit pull_unit(const TpGemmParams& p, int u, int upc,
+                                                       size_t part_bytes) {
+  CommUnit cu;
+  const int c = u / upc;                               // chunk in fetch order
+  const int stage = c / (p.world - 1);
+  const int pi = c - stage * (p.world - 1);
+  int src = p.rank + 1 + pi;
+  src = src >= p.world ? src - p.world : src;
+  cu.src = src;
+  cu.chunk = stage;
+  cu.begin = static_cast<uint32_t>(u - c * upc) * kPushUnit;
+  const uint32_t lim = cu.begin + static_cast<uint32_t>(kPushUnit);
+  cu.end = lim < p.chunk_bytes ? lim : p.chunk_bytes;
+  cu.base = static_cast<size_t>(src) * part_bytes + static_cast<size_t>(stage) * p.chunk_bytes;
+  return cu;
+}
+
 // Register-path PULL counterpart of comm_warp_push_regs: the units of all peers' chunks, in
 // arrival order, are dealt round-robin to the comm warps; each is read from the peer's
 // gathered buffer into registers and stored locally, then the local chunk counter is bumped.
@@ -479,14 +506,12 @@ __device__ __forceinline__ void comm_warp_pull_regs(const TpGemmParams& p, int g
   __syncwarp();
 
   for (int u = gw; u < total; u += nw) {
-    const int c = u / upc;                               // chunk in fetch order
-    const int stage = c / (p.world - 1);
-    const int pi = c - stage * (p.world - 1);
-    int src = p.rank + 1 + pi;
-    src = src >= p.world ? src - p.world : src;
-    const uint32_t begin = static_cast<uint32_t>(u - c * upc) * kPushUnit;
-    const uint32_t end = min(begin + static_cast<uint32_t>(kPushUnit), p.chunk_bytes);
-    const size_t base = static_cast<size_t>(src) * part_bytes + static_cast<size_t>(stage) * p.chunk_bytes;
+    const CommUnit cu = pull_unit(p, u, upc, part_bytes);
+    const int src = cu.src;
+    const int stage = cu.chunk;
+    const uint32_t begin = cu.begin;
+    const uint32_t end = cu.end;
+    const size_t base = cu.base;
     const uint8_t* from = p.peer_a[src] + base;
     for (uint32_t off = begin + lane * 16; off < end; off += 32 * 16 * kPushUnroll) {
       uint4 v[kPushUnroll];

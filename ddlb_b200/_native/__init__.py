@@ -83,6 +83,7 @@ def lib() -> ctypes.CDLL:
     L.ddlb_tp_gemm_run_emulated_static.argtypes = [POINTER(c_void_p), c_int, c_uint32, c_void_p]
     L.ddlb_debug_schedule.argtypes = [POINTER(TpGemmConfig), POINTER(c_int32 * 12)]
     L.ddlb_debug_tile_coords.argtypes = [POINTER(TpGemmConfig), c_int32, c_int32, POINTER(c_int32)]
+    L.ddlb_debug_pull_units.argtypes = [POINTER(TpGemmConfig), c_int64, POINTER(c_int64), POINTER(c_int64)]
     L.ddlb_copy.argtypes = [c_void_p, c_void_p, c_int64, c_int, c_void_p]
     L.ddlb_read_error_word.argtypes = [POINTER(c_uint32 * 4)]
     _lib = L

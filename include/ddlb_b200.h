@@ -137,6 +137,9 @@ int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int world, uint3
  * kernel's own tile_coord() evaluated for tiles [first, first+count). No reference counterpart. */
 int ddlb_debug_schedule(const ddlb_tp_gemm_config* cfg, int32_t out[12]);
 int ddlb_debug_tile_coords(const ddlb_tp_gemm_config* cfg, int32_t first, int32_t count, int32_t* out);
+/* units {src, chunk, begin, end, base} moved by the default AG_BEFORE transport of cfg->rank;
+ * pass out = NULL to get the count */
+int ddlb_debug_pull_units(const ddlb_tp_gemm_config* cfg, int64_t cap, int64_t* out, int64_t* count);
 
 /* Diagnostic: copy `bytes` (multiple of 16) with a 128-bit load/store kernel on `blocks` CTAs
  * (0 = 4 per SM). With a peer-mapped src it measures pull bandwidth, with a peer-mapped dst push. */

@@ -137,3 +137,44 @@ def test_fp32_geometry_resolves():
     assert s["num_n_blocks"] == 1
     with pytest.raises(N.NativeError, match="multiple of 32"):
         _schedule(_cfg("plain", 1, 0, 512, 80, 36, dtype=N.DTYPE_F32))
+
+
+@settings(max_examples=150, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(st.sampled_from([2, 3, 4, 8]), st.integers(1, 6), st.sampled_from([8, 72, 256, 1000, 1024]),
+       st.sampled_from([1, 2]), st.integers(0, 5), st.data())
+def test_comm_units_tile_every_peer_shard_exactly_once(world, mult, k, g, chunk_sel, data):
+    """Default AG_before transport: the units produced by the kernel's ``pull_unit`` cover every
+    byte of every peer's shard exactly once, in chunk order, and never touch the own shard."""
+    rank = data.draw(st.integers(0, world - 1))
+    tile_m = 128 * g
+    part_rows = mult * tile_m
+    chunk_rows = 0
+    if chunk_sel:
+        divisors = [d for d in range(1, mult + 1) if mult % d == 0]
+        chunk_rows = divisors[chunk_sel % len(divisors)] * tile_m
+    cfg = _cfg("ag_before", world, rank, part_rows * world, 64, k, cta_group=g, chunk_rows=chunk_rows)
+    sched = _schedule(cfg)
+    lib = N.lib()
+    count = ctypes.c_int64(0)
+    N.check(lib.ddlb_debug_pull_units(ctypes.byref(cfg), 0, None, ctypes.byref(count)), "units")
+    buf = (ctypes.c_int64 * (5 * count.value))()
+    N.check(lib.ddlb_debug_pull_units(ctypes.byref(cfg), count.value, buf, ctypes.byref(count)), "units")
+    units = [tuple(buf[5 * i:5 * i + 5]) for i in range(count.value)]
+    row_bytes = k * 2
+    part_bytes = part_rows * row_bytes
+    chunk_bytes = sched["chunk_rows"] * row_bytes
+    covered = {}
+    last_stage = -1
+    for src, chunk, begin, end, base in units:
+        assert src != rank and 0 <= src < world
+        assert 0 <= begin < end <= chunk_bytes and begin % 16 == 0 and end % 16 == 0
+        assert base == src * part_bytes + chunk * chunk_bytes
+        assert chunk >= last_stage                 # stage-major: chunk j of all peers before j+1
+        last_stage = chunk
+        covered.setdefault(src, []).append((base + begin, base + end))
+    assert sorted(covered) == [p for p in range(world) if p != rank]
+    for src, spans in covered.items():
+        spans.sort()
+        assert spans[0][0] == src * part_bytes and spans[-1][1] == (src + 1) * part_bytes
+        for (a0, a1), (b0, b1) in zip(spans, spans[1:]):
+            assert a1 == b0                        # contiguous, no gap, no overlap
