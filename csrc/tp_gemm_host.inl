@@ -209,6 +209,34 @@ static int select_kernel(ddlb_tp_gemm_plan* plan) {
     }
     return set_error("tracing is compiled for fp16/bf16, cta_group=2, block_n=256, B [k,n] only");
   }
+  if (plan->cfg.variant != 0) {
+    // experimental schedule variants: flagship configuration only (16-bit, cta_group 2, BN 256)
+    if (!(plan->res.elem == 2 && g == 2 && bn == 256 && nm))
+      return set_error("variants are compiled for fp16/bf16, cta_group=2, block_n=256, B [k,n] only");
+    using Cfg = TpGemmCfg<2, 256>;
+    void (*k)(TpGemmParams) = nullptr;
+    void (*ke)(const TpGemmParams*, int) = nullptr;
+    switch (plan->cfg.variant) {
+      case 1: k = tp_gemm_kernel<2, 256, true, false, false, 1>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 1>; break;
+      case 2: k = tp_gemm_kernel<2, 256, true, false, false, 2>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 2>; break;
+      case 3: k = tp_gemm_kernel<2, 256, true, false, false, 3>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 3>; break;
+      default: return set_error("unknown variant %d", plan->cfg.variant);
+    }
+    plan->kernel = k;
+    plan->emu_kernel = ke;
+    for (const void* f : {reinterpret_cast<const void*>(k), reinterpret_cast<const void*>(ke)}) {
+      cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+      if (e != cudaSuccess) { (void)cudaGetLastError(); return set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
+    }
+    (void)cudaFuncSetAttribute(reinterpret_cast<const void*>(k), cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    (void)cudaGetLastError();
+    const int fixed = 1024 + kEpiBytes + Cfg::kBarBytes + (plan->res.comm_in_cta == 1 ? kWarpRingBytes : 0);
+    int stages = (227 * 1024 - fixed) / Cfg::kStageBytes;
+    if (stages > Cfg::kStages) stages = Cfg::kStages;
+    plan->stages = stages;
+    plan->smem_bytes = fixed + stages * Cfg::kStageBytes;
+    return 0;
+  }
   if (plan->res.elem == 4) {      // fp32 through kind::tf32
     if (g == 1 && bn == 256) return nm ? bind_kernel<1, 256, true, true>(plan) : bind_kernel<1, 256, false, true>(plan);
     if (g == 2 && bn == 256) return nm ? bind_kernel<2, 256, true, true>(plan) : bind_kernel<2, 256, false, true>(plan);

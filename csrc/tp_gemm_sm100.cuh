@@ -571,7 +571,11 @@ struct Tracer {
 // kF32: fp32 inputs and outputs through kind::tf32 (operands are read as TF32 by the tensor
 // core, fp32 accumulation). A 128-byte swizzle row then holds 32 elements and one MMA covers
 // 8 of them, so the byte geometry of the operand ring is identical to the 16-bit case.
-template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kTrace = false>
+// kVariant: experimental schedule variants compiled as separate instantiations (bit 0: RS
+// announces a pushed tile as soon as its stores have completed instead of at the next tile;
+// bit 1: RS own-tile epilogue issues the staged-partial loads of two sources before adding).
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kTrace = false,
+          int kVariant = 0>
 __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cluster,
                                              const int nclusters) {
   using Cfg = TpGemmCfg<kCtaGroup, kBlockN>;
@@ -852,6 +856,31 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
 
         if (rs_own) {
           const int lr = local_row + lane;
+          if constexpr ((kVariant & 2) != 0) {
+            // two sources in flight: 16 independent 16-byte loads before the first add
+            const size_t col = static_cast<size_t>(n0 + c * 64);
+            for (int i = 1; i < p.world; i += 2) {
+              int s0 = p.rank + i, s1 = p.rank + i + 1;
+              s0 = s0 >= p.world ? s0 - p.world : s0;
+              s1 = s1 >= p.world ? s1 - p.world : s1;
+              const bool two = i + 1 < p.world;
+              const size_t row0 = static_cast<size_t>(parity * p.world + s0) * p.part_rows + lr;
+              const size_t row1 = static_cast<size_t>(parity * p.world + (two ? s1 : s0)) * p.part_rows + lr;
+              const uint4* src0 = reinterpret_cast<const uint4*>(p.stage_local + (row0 * p.out_n + col) * 2);
+              const uint4* src1 = reinterpret_cast<const uint4*>(p.stage_local + (row1 * p.out_n + col) * 2);
+              uint4 r0[8], r1[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) r0[j] = __ldcg(src0 + j);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) r1[j] = __ldcg(src1 + j);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) add_packed8(&v[8 * j], r0[j], bf16);
+              if (two) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) add_packed8(&v[8 * j], r1[j], bf16);
+              }
+            }
+          } else {
           for (int s = 0; s < p.world; ++s) {
             if (s == p.rank) continue;
             const size_t row = static_cast<size_t>(parity * p.world + s) * p.part_rows + lr;
@@ -862,6 +891,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
               const uint4 raw = __ldcg(src + j);
               add_packed8(&v[8 * j], raw, bf16);
             }
+          }
           }
         }
 
@@ -902,8 +932,17 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         else mbar_arrive(bar_tempty + acc * 8);
       }
       tr.ev(kEvTileStored, static_cast<uint32_t>(t));
+      if constexpr ((kVariant & 1) != 0) {
+        if (rs_push && lane == 0) {
+          // announce now: the accumulator is already released, only this warp waits
+          bulk_wait<0>();
+          fence_proxy_async();
+          red_add_release_sys(p.sig_peer[tc.part] + p.rs_sig_off + p.rank * p.rs_tiles_per_src + cta_tile, 1u);
+        }
+      } else {
       if (rs_push)
         pending_sig = p.sig_peer[tc.part] + p.rs_sig_off + p.rank * p.rs_tiles_per_src + cta_tile;
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
     if (lane == 0) {
@@ -935,25 +974,26 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
 }
 
 // One rank per process / GPU: parameters in the kernel parameter space.
-template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kTrace = false>
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kTrace = false,
+          int kVariant = 0>
 __global__ void __launch_bounds__(kNumThreads, 1)
 tp_gemm_kernel(const __grid_constant__ TpGemmParams p) {
   const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
   const int nclusters = kCtaGroup == 2 ? static_cast<int>(num_clusters_x()) : static_cast<int>(gridDim.x);
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kTrace>(p, cluster, nclusters);
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kTrace, kVariant>(p, cluster, nclusters);
 }
 
 // Several ranks emulated by ONE launch on one GPU (tests): the grid is split into
 // `world` equal groups of clusters, group r runs rank r's parameter block. All
 // CTAs of one launch are co-resident (grid <= SM count), so ranks that wait on
 // each other make progress, which separate launches on one GPU cannot guarantee.
-template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false>
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, int kVariant = 0>
 __global__ void __launch_bounds__(kNumThreads, 1)
 tp_gemm_emulated_kernel(const TpGemmParams* __restrict__ plist, int clusters_per_rank) {
   const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
   const int vr = cluster / clusters_per_rank;
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32>(plist[vr], cluster - vr * clusters_per_rank,
-                                                   clusters_per_rank);
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, false, kVariant>(
+      plist[vr], cluster - vr * clusters_per_rank, clusters_per_rank);
 }
 
 }  // namespace ddlb

@@ -40,6 +40,7 @@ class TpGemmConfig(Structure):
         ("stage_local", c_void_p),
         ("sig_local", c_void_p), ("sig_peer", c_void_p * MAX_WORLD),
         ("trace", c_void_p),
+        ("variant", c_int32), ("reserved", c_int32),
     ]
 
 

@@ -258,7 +258,7 @@ class FusedGemmReduceScatter(_FusedBase):
 
     def __init__(self, heap, rank: int, world: int, m: int, n: int, k: int, dtype, a, b,
                  chunk_rows: int = 0, cta_group: int = 0, block_n: int = 0, group_m: int = 0,
-                 num_sms: int = 0, b_is_nk: bool = False, trace: bool = False):
+                 num_sms: int = 0, b_is_nk: bool = False, trace: bool = False, variant: int = 0):
         super().__init__(heap, rank, world)
         import torch
         self.trace_buf = None
@@ -285,6 +285,7 @@ class FusedGemmReduceScatter(_FusedBase):
             cfg.stage_local = heap.ptr(st_off)
             self._alloc_signals(cfg)
         cfg.a, cfg.b = a.data_ptr(), b.data_ptr()
+        cfg.variant = int(variant)            # experimental A/B schedule variants (0 = production)
         if self.trace_buf is not None:
             cfg.trace = self.trace_buf.data_ptr()
         self.plan = TpGemmPlan(cfg, keepalive=(a, b, self.out))

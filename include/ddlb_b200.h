@@ -91,6 +91,10 @@ typedef struct ddlb_tp_gemm_config {
    * records of 16 bytes {tag, arg, time_lo, time_hi (globaltimer ns)}, zero-initialised by the
    * caller. Only for fp16/bf16, cta_group 2, block_n 256, B [k,n]. No reference counterpart. */
   void* trace;
+  /* experimental schedule variant (0 = production kernel). RS: bit 0 announces a pushed tile
+   * immediately, bit 1 loads two staged partials at a time. Flagship configuration only. */
+  int32_t variant;
+  int32_t reserved;
 } ddlb_tp_gemm_config;
 #define DDLB_TRACE_ROLES 4
 #define DDLB_TRACE_SLOTS 128
