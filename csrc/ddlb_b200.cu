@@ -44,3 +44,4 @@ extern "C" int ddlb_version(void) { return 100; }
 #include "tp_gemm_sm100.cuh"
 #include "tp_gemm_host.inl"
 #include "runtime.inl"
+#include "vmm_heap.inl"

@@ -226,3 +226,21 @@ extern "C" int ddlb_copy(void* dst, const void* src, int64_t bytes, int blocks, 
   DDLB_CUDA(cudaGetLastError());
   return 0;
 }
+
+// Barrier on caller-provided signal pads (one pad base per rank, as seen from this process):
+// the same kernel as ddlb_symm_barrier for heaps that are not ddlb_symm objects (VMM heap).
+extern "C" int ddlb_barrier_raw(void* const* pad_bases, int rank, int world, uint32_t epoch, void* stream) {
+  using namespace ddlb;
+  if (pad_bases == nullptr || world < 1 || world > DDLB_MAX_WORLD || rank < 0 || rank >= world)
+    return set_error("bad arguments");
+  if (world == 1) return 0;
+  uint32_t* sig[8] = {};
+  for (int p = 0; p < world; ++p) {
+    if (pad_bases[p] == nullptr) return set_error("pad of rank %d is null", p);
+    sig[p] = static_cast<uint32_t*>(pad_bases[p]);
+  }
+  barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(
+      sig[rank], nullptr, sig[0], sig[1], sig[2], sig[3], sig[4], sig[5], sig[6], sig[7], rank, world, epoch);
+  DDLB_CUDA(cudaGetLastError());
+  return 0;
+}

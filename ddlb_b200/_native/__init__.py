@@ -85,6 +85,26 @@ def lib() -> ctypes.CDLL:
     L.ddlb_debug_schedule.argtypes = [POINTER(TpGemmConfig), POINTER(c_int32 * 12)]
     L.ddlb_debug_tile_coords.argtypes = [POINTER(TpGemmConfig), c_int32, c_int32, POINTER(c_int32)]
     L.ddlb_debug_pull_units.argtypes = [POINTER(TpGemmConfig), c_int64, POINTER(c_int64), POINTER(c_int64)]
+    c_int_p = POINTER(c_int)
+    L.ddlb_vmm_multicast_supported.argtypes = [c_int, c_int_p]
+    L.ddlb_vmm_create.argtypes = [c_int, c_int, c_int, c_int64, POINTER(c_void_p)]
+    L.ddlb_vmm_export_fd.argtypes = [c_void_p, c_int_p]
+    L.ddlb_vmm_import_peer.argtypes = [c_void_p, c_int, c_int]
+    L.ddlb_vmm_mc_create.argtypes = [c_void_p, c_int_p]
+    L.ddlb_vmm_mc_import.argtypes = [c_void_p, c_int]
+    L.ddlb_vmm_mc_add_device.argtypes = [c_void_p]
+    L.ddlb_vmm_mc_bind.argtypes = [c_void_p]
+    L.ddlb_vmm_base.argtypes = [c_void_p, c_int]
+    L.ddlb_vmm_base.restype = c_void_p
+    L.ddlb_vmm_mc_base.argtypes = [c_void_p]
+    L.ddlb_vmm_mc_base.restype = c_void_p
+    L.ddlb_vmm_bytes.argtypes = [c_void_p]
+    L.ddlb_vmm_bytes.restype = c_int64
+    L.ddlb_vmm_selftest_store.argtypes = [c_void_p, c_int64, c_int, c_void_p]
+    L.ddlb_vmm_selftest_reduce.argtypes = [c_void_p, c_int64, c_void_p, c_int, c_void_p]
+    L.ddlb_vmm_destroy.argtypes = [c_void_p]
+    L.ddlb_vmm_has_multicast.argtypes = [c_void_p]
+    L.ddlb_barrier_raw.argtypes = [POINTER(c_void_p), c_int, c_int, c_uint32, c_void_p]
     L.ddlb_copy.argtypes = [c_void_p, c_void_p, c_int64, c_int, c_void_p]
     L.ddlb_read_error_word.argtypes = [POINTER(c_uint32 * 4)]
     _lib = L

@@ -194,8 +194,12 @@ class Communicator:
         if not self.is_cuda:
             raise RuntimeError("the symmetric heap needs CUDA devices")
         if self._symm is None:
-            from .parallel.symm_heap import SymmetricHeap
-            self._symm = SymmetricHeap(self, min_bytes)
+            if os.environ.get("DDLB_SYMM_MODE", "ipc") == "vmm":     # experimental, see vmm_heap.py
+                from .parallel.vmm_heap import VmmHeap
+                self._symm = VmmHeap(self, min_bytes)
+            else:
+                from .parallel.symm_heap import SymmetricHeap
+                self._symm = SymmetricHeap(self, min_bytes)
         elif min_bytes > self._symm.capacity:
             raise RuntimeError(
                 f"symmetric heap already created with {self._symm.capacity} B; "

@@ -47,6 +47,35 @@ int ddlb_symm_destroy(ddlb_symm* s);
  * the dummy all_reduce of ddlb/benchmark.py:134-137, ddlb/communicator.py:74).
  * Asynchronous on `stream`; every rank must call it the same number of times. */
 int ddlb_symm_barrier(ddlb_symm* s, void* stream);
+/* the same barrier on caller-provided pads: pad_bases[r] = rank r's pad as mapped here; epoch
+ * = 1, 2, 3, ... per call, identical on all ranks */
+int ddlb_barrier_raw(void* const* pad_bases, int rank, int world, uint32_t epoch, void* stream);
+
+/* ------------------------------------------- VMM heap + NVLS multicast (EXPERIMENTAL)
+ * Same role as ddlb_symm_* but on cuMemCreate/cuMemMap with POSIX file-descriptor handles and,
+ * where the devices support it, a multicast object (multimem.st / multimem.ld_reduce through
+ * the NVSwitch). Written after round 1's GPU budget was spent: compiled, never run. Protocol:
+ *   every rank: ddlb_vmm_create; ddlb_vmm_export_fd -> send fd to peers; ddlb_vmm_import_peer
+ *   rank 0: ddlb_vmm_mc_create -> send fd; others: ddlb_vmm_mc_import
+ *   every rank: ddlb_vmm_mc_add_device; HOST BARRIER; ddlb_vmm_mc_bind
+ * Counterpart in the reference: nvFuser's "cuda" backend with multicast_protocol=multimem
+ * (ddlb/primitives/TPColumnwise/fuser.py:171-206), which lives outside the reference repo. */
+typedef struct ddlb_vmm ddlb_vmm;
+int ddlb_vmm_multicast_supported(int device, int* supported);
+int ddlb_vmm_create(int device, int rank, int world, int64_t bytes, ddlb_vmm** out);
+int ddlb_vmm_export_fd(ddlb_vmm* s, int* fd);
+int ddlb_vmm_import_peer(ddlb_vmm* s, int peer, int fd);
+int ddlb_vmm_mc_create(ddlb_vmm* s, int* fd);
+int ddlb_vmm_mc_import(ddlb_vmm* s, int fd);
+int ddlb_vmm_mc_add_device(ddlb_vmm* s);
+int ddlb_vmm_mc_bind(ddlb_vmm* s);
+void* ddlb_vmm_base(ddlb_vmm* s, int rank);
+void* ddlb_vmm_mc_base(ddlb_vmm* s);
+int64_t ddlb_vmm_bytes(ddlb_vmm* s);
+int ddlb_vmm_selftest_store(ddlb_vmm* s, int64_t offset, int n_per_rank, void* stream);
+int ddlb_vmm_selftest_reduce(ddlb_vmm* s, int64_t offset, float* out, int n, void* stream);
+int ddlb_vmm_has_multicast(ddlb_vmm* s);
+int ddlb_vmm_destroy(ddlb_vmm* s);
 
 /* --------------------------------------------------------------- fused GEMM */
 enum { DDLB_MODE_PLAIN = 0, DDLB_MODE_AG_BEFORE = 1, DDLB_MODE_AG_AFTER = 2, DDLB_MODE_RS = 3 };

@@ -10,6 +10,8 @@ echo "=== bench ours N=2"
 timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus 2 --steps 100 --warmup 10 2>gpurun_out/bench_ours_2.err | tee gpurun_out/bench_ours_n2.json | cut -c1-400
 echo "=== rowwise variants A/B (after they passed in emulation)"
 timeout 200 python -m ddlb_b200.launcher -np 2 --timeout 180 scripts/dev/r2_rowwise_ab.py 2>&1 | grep variant
+echo "=== VMM heap + multicast self-test"
+DDLB_RUN_EXPERIMENTAL=1 timeout 200 python -m pytest tests/test_vmm_experimental_gpu.py -q -s 2>&1 | tail -12
 echo "=== multigpu tests"
 timeout 300 python -m pytest tests/test_multigpu.py -x -q -k "2" 2>&1 | tail -4
 } 2>&1 | tee gpurun_out/r2_session1.log
