@@ -73,6 +73,8 @@ def describe_implementation(impl_class, base_impl: str, options: Dict[str, Any])
 
 
 def _empty_row(label, option_str, m, n, k, dtype, backend, barrier, validate, error):
+    """A result row with the reference's columns in the reference's order
+    (``REFERENCE_COLUMNS``), ``valid`` when validating, then ``EXTRA_COLUMNS``."""
     row = {
         "implementation": label, "mean_time (ms)": float("nan"), "std_time": float("nan"),
         "min_time": float("nan"), "max_time": float("nan"), "m": m, "n": n, "k": k,
@@ -86,6 +88,8 @@ def _empty_row(label, option_str, m, n, k, dtype, backend, barrier, validate, er
     row.update({"roofline_ms": float("nan"), "pct_roofline": float("nan"),
                 "flops_per_gpu": float("nan"), "comm_bytes_per_gpu": float("nan"),
                 "error": error})
+    expected = REFERENCE_COLUMNS + (["valid"] if validate else []) + EXTRA_COLUMNS
+    assert list(row) == expected, "result-row schema drifted from the documented column order"
     return row
 
 

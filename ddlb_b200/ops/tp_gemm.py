@@ -12,9 +12,6 @@ from typing import Dict, List, Optional, Sequence
 
 from .. import _native as N
 
-_DTYPES = {"float16": N.DTYPE_F16, "bfloat16": N.DTYPE_BF16}
-
-
 def _dtype_code(t) -> int:
     import torch
     if t == torch.float16:
@@ -141,10 +138,11 @@ class _FusedBase:
 class FusedAllGatherGemm(_FusedBase):
     """``C[m,n] = allgather_rows(A_shard)[m,k] @ B[k,n]`` in ONE kernel per rank.
 
-    ``order="AG_before"``: comm CTAs pull the peers' shards over NVLink into the local
-    gathered buffer chunk by chunk while GEMM CTAs multiply the chunks that have
-    arrived. ``order="AG_after"``: each rank multiplies its own shard and its
-    epilogue stores the C tiles into every rank's output.
+    ``order="AG_before"``: the peers' shards are moved over NVLink into the local gathered
+    buffer chunk by chunk (``transport``: by two warps of every CTA through registers, by a
+    TMA warp per CTA, or by dedicated comm CTAs) while the GEMM multiplies the chunks that
+    have arrived. ``order="AG_after"``: each rank multiplies its own shard and its epilogue
+    stores the C tiles into every rank's output.
     The rank's input shard must be written into ``self.a_shard`` (a view of the
     symmetric gathered buffer).
     """
@@ -164,7 +162,6 @@ class FusedAllGatherGemm(_FusedBase):
             raise ValueError(f"transport must be one of {sorted(transports)}, got {transport!r}")
         rows = m // world
         self.order = order
-        elt = torch.empty((), dtype=dtype).element_size()
         layout = N.B_NK if b_is_nk else N.B_KN
         if order == "AG_before":
             self.out = [torch.empty(m, n, dtype=dtype, device=b.device)]
