@@ -220,6 +220,8 @@ static int select_kernel(ddlb_tp_gemm_plan* plan) {
       case 1: k = tp_gemm_kernel<2, 256, true, false, false, 1>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 1>; break;
       case 2: k = tp_gemm_kernel<2, 256, true, false, false, 2>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 2>; break;
       case 3: k = tp_gemm_kernel<2, 256, true, false, false, 3>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 3>; break;
+      case 4: k = tp_gemm_kernel<2, 256, true, false, false, 4>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 4>; break;
+      case 6: k = tp_gemm_kernel<2, 256, true, false, false, 6>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 6>; break;
       default: return set_error("unknown variant %d", plan->cfg.variant);
     }
     plan->kernel = k;
@@ -376,6 +378,7 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   p.sig_local = c.sig_local;
   p.sig_peer[c.rank] = c.sig_local;
   p.trace = static_cast<uint4*>(c.trace);
+  for (int d = 0; d < c.world; ++d) p.out_raw[d] = static_cast<uint8_t*>(c.out[d]);
   *out = plan;
   return 0;
 }

@@ -86,6 +86,8 @@ struct TpGemmParams {
   uint32_t* sig_peer[kMaxWorld];
   // optional device trace (kTrace kernels only): [cta][role][kTraceSlots] x {tag, arg, time ns}
   uint4* trace;
+  // raw output addresses (same buffers as tmOut[]), used by the register-store push variant
+  uint8_t* out_raw[kMaxWorld];
 };
 
 template <int kCtaGroup, int kBlockN>
@@ -568,12 +570,41 @@ struct Tracer {
   }
 };
 
+// Store one staged epilogue chunk (32 rows x 128 bytes, 128-byte swizzled in shared memory)
+// with 128-bit stores: per instruction the warp writes 4 rows x 128 contiguous bytes. Used by
+// the push variant for PEER destinations, where plain stores move ~690 GB/s over NVLink and
+// TMA stores were measured at ~400-530 GB/s.
+__device__ __forceinline__ void store_chunk_st128(uint8_t* dst_base, size_t pitch_bytes, int row0,
+                                                  int col_byte0, int row_limit, int col_limit_bytes,
+                                                  uint32_t sbase, int lane) {
+#pragma unroll
+  for (int it = 0; it < 8; ++it) {
+    const int r = it * 4 + (lane >> 3);
+    const int j = lane & 7;
+    uint4 v;
+    const uint32_t src = sbase + r * 128 + (static_cast<uint32_t>(j ^ (r & 7)) << 4);
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "r"(src)
+                 : "memory");
+    const int colb = col_byte0 + j * 16;
+    if (row0 + r < row_limit && colb < col_limit_bytes) {
+      uint4* dst = reinterpret_cast<uint4*>(dst_base + static_cast<size_t>(row0 + r) * pitch_bytes + colb);
+      asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(v.x), "r"(v.y), "r"(v.z),
+                   "r"(v.w)
+                   : "memory");
+    }
+  }
+}
+
 // kF32: fp32 inputs and outputs through kind::tf32 (operands are read as TF32 by the tensor
 // core, fp32 accumulation). A 128-byte swizzle row then holds 32 elements and one MMA covers
 // 8 of them, so the byte geometry of the operand ring is identical to the 16-bit case.
 // kVariant: experimental schedule variants compiled as separate instantiations (bit 0: RS
 // announces a pushed tile as soon as its stores have completed instead of at the next tile;
-// bit 1: RS own-tile epilogue issues the staged-partial loads of two sources before adding).
+// bit 1: RS own-tile epilogue issues the staged-partial loads of two sources before adding;
+// bit 2: tiles pushed to PEERS (RS, AG_AFTER) are written with 128-bit stores from the staged
+// shared-memory rows instead of TMA stores).
 template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kTrace = false,
           int kVariant = 0>
 __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cluster,
@@ -913,6 +944,29 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         }
         fence_proxy_async_smem();
         __syncwarp();
+        if constexpr ((kVariant & 4) != 0) {
+          // push variant: peers are written with 128-bit stores from the staged rows, only
+          // local destinations go through TMA
+          const size_t pitch = static_cast<size_t>(p.out_n) * 2;
+          const int colb = (n0 + c * 64) * 2;
+          if (rs_push) {
+            store_chunk_st128(p.out_raw[tc.part], pitch, out_row, colb, 2 * p.world * p.part_rows,
+                              p.out_n * 2, sbase, lane);
+          } else if (p.mode == kModeAGAfter) {
+            for (int d = 0; d < p.world; ++d)
+              if (d != p.rank)
+                store_chunk_st128(p.out_raw[d], pitch, out_row, colb, p.world * p.part_rows,
+                                  p.out_n * 2, sbase, lane);
+            if (lane == 0) {
+              tma_store_2d(&p.tmOut[p.rank], sbase, n0 + c * 64, out_row);
+              bulk_commit();
+            }
+          } else if (lane == 0) {
+            tma_store_2d(&p.tmOut[p.mode == kModeRS ? tc.part : p.rank], sbase, n0 + c * 64, out_row);
+            bulk_commit();
+          }
+          __syncwarp();            // every lane has read the staged rows before they are reused
+        } else {
         if (lane == 0) {
           if (p.mode == kModeAGAfter) {
             for (int d = 0; d < p.world; ++d) tma_store_2d(&p.tmOut[d], sbase, n0 + c * 64, out_row);
@@ -921,6 +975,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
             tma_store_2d(&p.tmOut[p.mode == kModeRS ? tc.part : p.rank], sbase, n0 + c * 64, out_row);
           }
           bulk_commit();
+        }
         }
         buf ^= 1;
       }
@@ -932,7 +987,14 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         else mbar_arrive(bar_tempty + acc * 8);
       }
       tr.ev(kEvTileStored, static_cast<uint32_t>(t));
-      if constexpr ((kVariant & 1) != 0) {
+      if constexpr ((kVariant & 4) != 0) {
+        if (rs_push) {
+          __threadfence_system();          // this lane's peer stores are performed
+          __syncwarp();
+          if (lane == 0)
+            red_add_release_sys(p.sig_peer[tc.part] + p.rs_sig_off + p.rank * p.rs_tiles_per_src + cta_tile, 1u);
+        }
+      } else if constexpr ((kVariant & 1) != 0) {
         if (rs_push && lane == 0) {
           // announce now: the accumulator is already released, only this warp waits
           bulk_wait<0>();
@@ -956,6 +1018,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     if (p.mode == kModeAGAfter && p.world > 1) {
       // every CTA tells every peer that its share of C has landed, then waits for
       // all CTAs of all peers so that C is complete when this kernel ends
+      if constexpr ((kVariant & 4) != 0) __threadfence_system();
       if (lane == 0) { fence_proxy_async(); fence_acq_rel_sys(); }
       named_bar_sync(1, 128);
       if (warp == 4 && lane < p.world && lane != p.rank) {

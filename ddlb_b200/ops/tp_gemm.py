@@ -150,7 +150,8 @@ class FusedAllGatherGemm(_FusedBase):
     def __init__(self, heap, rank: int, world: int, m: int, n: int, k: int, dtype, b,
                  order: str = "AG_before", chunk_rows: int = 0, n_comm_ctas: int = 0,
                  cta_group: int = 0, block_n: int = 0, group_m: int = 0, num_sms: int = 0,
-                 b_is_nk: bool = False, transport: str = "cta_pull", trace: bool = False):
+                 b_is_nk: bool = False, transport: str = "cta_pull", trace: bool = False,
+                 variant: int = 0):
         super().__init__(heap, rank, world)
         import torch
         if m % world:
@@ -211,6 +212,7 @@ class FusedAllGatherGemm(_FusedBase):
             self.trace_buf = alloc_trace_buffer(b.device)
         for c in cfgs:
             c.b = b.data_ptr()
+            c.variant = int(variant)          # experimental A/B schedule variants (0 = production)
             if self.trace_buf is not None:
                 c.trace = self.trace_buf.data_ptr()
         if world > 1:

@@ -121,7 +121,9 @@ typedef struct ddlb_tp_gemm_config {
    * caller. Only for fp16/bf16, cta_group 2, block_n 256, B [k,n]. No reference counterpart. */
   void* trace;
   /* experimental schedule variant (0 = production kernel). RS: bit 0 announces a pushed tile
-   * immediately, bit 1 loads two staged partials at a time. Flagship configuration only. */
+   * immediately, bit 1 loads two staged partials at a time, bit 2 (RS and AG_AFTER) pushes tiles
+   * to peers with 128-bit stores instead of TMA stores. Values 1, 2, 3, 4, 6. Flagship
+   * configuration only. */
   int32_t variant;
   int32_t reserved;
 } ddlb_tp_gemm_config;

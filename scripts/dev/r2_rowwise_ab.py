@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Round-2 A/B of the tp_rowwise schedule variants on real GPUs (launch with the in-tree
-launcher, 2 or 8 ranks): production kernel vs variants 1, 2, 3, CUDA-event timed behind the
+launcher, 2 or 8 ranks): production kernel vs variants 1, 2, 3, 4, 6, CUDA-event timed behind the
 device barrier, max over ranks."""
 import os
 import sys
@@ -21,7 +21,7 @@ def main():
     torch.manual_seed(42)
     a = (2 * torch.rand(m, k // d, device=comm.device) - 1).to(dt)
     b = (2 * torch.rand(k // d, n, device=comm.device) - 1).to(dt)
-    for variant in (0, 1, 2, 3):
+    for variant in (0, 1, 2, 3, 4, 6):
         op = FusedGemmReduceScatter(heap, r, d, m, n, k, dt, a, b, cta_group=2, block_n=256,
                                     variant=variant)
         torch.cuda.synchronize()
