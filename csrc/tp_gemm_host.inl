@@ -46,10 +46,12 @@ static int make_tmap(CUtensorMap* map, void* base, int rank, const uint64_t* dim
 }
 
 struct Resolved {
-  int cta_group, block_n, group_m, grid, n_comm_ctas, chunk_rows;
+  int cta_group, block_n, group_m, grid, chunk_rows;
   int tile_m, part_rows, a_rows, kk;   // kk: contraction length seen by this kernel
-  int comm_in_cta;
-  int elem;   // bytes per element: 2 (fp16/bf16) or 4 (fp32 through TF32)
+  int elem;      // bytes per element: 2 (fp16/bf16) or 4 (fp32 through TF32)
+  int split;     // 1: 3xTF32 (fp32 only)
+  int threads;   // 256, or 384 when the aux warps 8..11 have work (collectives, 3xTF32)
+  int part0;     // first shard in visiting order
 };
 
 static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
@@ -59,6 +61,12 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
   if (c.dtype != DDLB_DTYPE_F16 && c.dtype != DDLB_DTYPE_BF16 && c.dtype != DDLB_DTYPE_F32)
     return set_error("bad dtype %d", c.dtype);
   r.elem = c.dtype == DDLB_DTYPE_F32 ? 4 : 2;
+  if (r.elem == 4 && c.b_layout != DDLB_B_ROW_MAJOR_NK)
+    return set_error("float32 needs B as [n,k] (DDLB_B_ROW_MAJOR_NK): the tensor cores read an "
+                     "N-major tf32 operand in a different shared-memory layout; transpose the "
+                     "weight once");
+  if (c.fp32_mode != DDLB_FP32_3XTF32 && c.fp32_mode != DDLB_FP32_TF32) return set_error("bad fp32_mode");
+  r.split = (r.elem == 4 && c.fp32_mode == DDLB_FP32_3XTF32) ? 1 : 0;
   const int row_elems = 128 / r.elem;          // elements per 128-byte swizzle row
   if (c.m <= 0 || c.n <= 0 || c.k <= 0) return set_error("bad shape");
   if (c.m % c.world != 0) return set_error("m (%lld) must be divisible by world (%d)", (long long)c.m, c.world);
@@ -81,7 +89,10 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
   if (sharded_rows && r.part_rows % r.tile_m != 0)
     return set_error("rows per rank (%d) must be a multiple of %d for the fused kernel", r.part_rows, r.tile_m);
   r.block_n = c.block_n != 0 ? c.block_n : (c.n <= 128 ? 128 : 256);
+  if (r.split && r.cta_group == 1 && c.block_n == 0) r.block_n = 128;   // hi+lo ring must fit
   if (r.block_n != 128 && r.block_n != 256) return set_error("block_n must be 128 or 256");
+  if (r.split && r.cta_group == 1 && r.block_n == 256)
+    return set_error("3xTF32 with cta_group=1 needs block_n=128 (shared memory)");
 
   int dev = 0, sms = 0;
   if (cudaGetDevice(&dev) != cudaSuccess ||
@@ -97,12 +108,11 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
 
   r.group_m = c.group_m > 0 ? c.group_m : 8;
 
-  r.n_comm_ctas = 0;
   r.chunk_rows = r.part_rows;
   if (c.mode == DDLB_MODE_AG_BEFORE || c.mode == DDLB_MODE_RS) {
     int cr = c.chunk_rows;
     if (cr <= 0) {
-      // auto: about 1 MiB of A per chunk (AG) / 4 tile rows (RS), dividing the shard evenly
+      // auto: about 1 MiB of A per chunk (AG) / the whole shard (RS), dividing the shard evenly
       const int mblks = r.part_rows / r.tile_m;
       int want = c.mode == DDLB_MODE_AG_BEFORE
                      ? static_cast<int>((1 << 20) / (static_cast<int64_t>(r.kk) * r.elem * r.tile_m))
@@ -116,29 +126,26 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
       return set_error("chunk_rows (%d) must be a multiple of %d and divide rows per rank (%d)", cr,
                        r.tile_m, r.part_rows);
     r.chunk_rows = cr;
-  }
-  r.comm_in_cta = 0;
-  if (c.mode == DDLB_MODE_AG_BEFORE && c.world > 1) {
-    if (c.comm_transport == DDLB_COMM_EVERY_CTA) r.comm_in_cta = 2;       // register push, warps 2+3
-    if (c.comm_transport == DDLB_COMM_EVERY_CTA_TMA) r.comm_in_cta = 1;   // TMA pull ring, warp 3
-    if (c.comm_transport == DDLB_COMM_EVERY_CTA_PULL) r.comm_in_cta = 3;  // register pull, warps 2+3
-  }
-  if (r.comm_in_cta) {
     const int64_t chunk_bytes = static_cast<int64_t>(r.chunk_rows) * r.kk * r.elem;
-    if (chunk_bytes > 0xffffffffll) return set_error("chunk too large");
+    if (c.mode == DDLB_MODE_AG_BEFORE && chunk_bytes > 0xffffffffll) return set_error("chunk too large");
   }
-  if (c.mode == DDLB_MODE_AG_BEFORE && c.world > 1 && !r.comm_in_cta) {
-    int nc = c.n_comm_ctas > 0 ? c.n_comm_ctas : 16;
-    nc -= nc % r.cta_group;
-    if (nc < r.cta_group) nc = r.cta_group;
-    const int64_t chunk_bytes = static_cast<int64_t>(r.chunk_rows) * r.kk * r.elem;
-    while (nc > r.cta_group && (chunk_bytes % (static_cast<int64_t>(nc) * 16) != 0)) nc -= r.cta_group;
-    if (chunk_bytes % (static_cast<int64_t>(nc) * 16) != 0)
-      return set_error("chunk of %lld bytes cannot be split over %d comm CTAs", (long long)chunk_bytes, nc);
-    if (nc >= r.grid) return set_error("n_comm_ctas (%d) leaves no CTA for the GEMM", nc);
-    if (chunk_bytes > 0xffffffffll) return set_error("chunk too large");
-    r.n_comm_ctas = nc;
+  if (c.ag_transport < 0 || c.ag_transport > 2) return set_error("bad ag_transport %d", c.ag_transport);
+  if (c.epi_transport < 0 || c.epi_transport > 2) return set_error("bad epi_transport %d", c.epi_transport);
+  if (c.rs_transport < 0 || c.rs_transport > 2) return set_error("bad rs_transport %d", c.rs_transport);
+  if (c.epilogue_act < 0 || c.epilogue_act > 3) return set_error("bad epilogue_act %d", c.epilogue_act);
+  if (c.epilogue_act != 0 && c.mode == DDLB_MODE_RS && c.world > 1)
+    return set_error("an epilogue activation cannot be applied to partial sums (tp_rowwise)");
+
+  // visiting order of the shards: AG starts with the own shard (it is already here), RS push
+  // ends with it (its partials need no NVLink); the pull reductions and the un-rotated
+  // order visit 0..d-1 on every rank so that a shard completes everywhere at the same time
+  r.part0 = 0;
+  if (!c.unrotated) {
+    if (c.mode == DDLB_MODE_AG_BEFORE) r.part0 = c.rank;
+    if (c.mode == DDLB_MODE_RS && c.rs_transport == DDLB_RS_PUSH) r.part0 = (c.rank + 1) % c.world;
   }
+  const bool collective = c.world > 1 && (c.mode == DDLB_MODE_AG_BEFORE || c.mode == DDLB_MODE_RS);
+  r.threads = (collective || r.split) ? kMaxThreads : kBaseThreads;
   return 0;
 }
 
@@ -156,22 +163,15 @@ struct ddlb_tp_gemm_plan {
 
 namespace ddlb {
 
-template <int G, int BN, bool NM, bool F32 = false>
+template <int G, int BN, bool NM, bool F32 = false, bool SPLIT = false>
 static int bind_kernel(ddlb_tp_gemm_plan* plan) {
-  using Cfg = TpGemmCfg<G, BN>;
-  auto k = tp_gemm_kernel<G, BN, NM, F32>;
+  using Cfg = TpGemmCfg<G, BN, SPLIT>;
+  auto k = tp_gemm_kernel<G, BN, NM, F32, SPLIT>;
   plan->kernel = reinterpret_cast<void (*)(TpGemmParams)>(k);
-  auto ke = tp_gemm_emulated_kernel<G, BN, NM, F32>;
+  auto ke = tp_gemm_emulated_kernel<G, BN, NM, F32, SPLIT>;
   plan->emu_kernel = ke;
-  {
-    // operand ring depth: whatever fits beside the epilogue buffers (and the comm warp's ring)
-    const int fixed = 1024 + kEpiBytes + Cfg::kBarBytes + (plan->res.comm_in_cta == 1 ? kWarpRingBytes : 0);
-    int stages = (227 * 1024 - fixed) / Cfg::kStageBytes;
-    if (stages > Cfg::kStages) stages = Cfg::kStages;
-    if (stages < 2) return set_error("shared memory too small for the operand ring");
-    plan->stages = stages;
-    plan->smem_bytes = fixed + stages * Cfg::kStageBytes;
-  }
+  plan->stages = Cfg::kStages;
+  plan->smem_bytes = Cfg::kSmemBytes;
   cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
   if (e == cudaSuccess)
     e = cudaFuncSetAttribute(ke, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
@@ -193,57 +193,30 @@ static int select_kernel(ddlb_tp_gemm_plan* plan) {
     // traced variant exists for the flagship configuration only (16-bit, cta_group 2, BN 256)
     if (plan->res.elem == 2 && g == 2 && bn == 256 && nm) {
       using Cfg = TpGemmCfg<2, 256>;
-      auto k = tp_gemm_kernel<2, 256, true, false, true>;
+      auto k = tp_gemm_kernel<2, 256, true, false, false, true>;
       plan->kernel = reinterpret_cast<void (*)(TpGemmParams)>(k);
       plan->emu_kernel = nullptr;
       cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
       if (e != cudaSuccess) { (void)cudaGetLastError(); return set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
       (void)cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
       (void)cudaGetLastError();
-      const int fixed = 1024 + kEpiBytes + Cfg::kBarBytes + (plan->res.comm_in_cta == 1 ? kWarpRingBytes : 0);
-      int stages = (227 * 1024 - fixed) / Cfg::kStageBytes;
-      if (stages > Cfg::kStages) stages = Cfg::kStages;
-      plan->stages = stages;
-      plan->smem_bytes = fixed + stages * Cfg::kStageBytes;
+      plan->stages = Cfg::kStages;
+      plan->smem_bytes = Cfg::kSmemBytes;
       return 0;
     }
     return set_error("tracing is compiled for fp16/bf16, cta_group=2, block_n=256, B [k,n] only");
   }
-  if (plan->cfg.variant != 0) {
-    // experimental schedule variants: flagship configuration only (16-bit, cta_group 2, BN 256)
-    if (!(plan->res.elem == 2 && g == 2 && bn == 256 && nm))
-      return set_error("variants are compiled for fp16/bf16, cta_group=2, block_n=256, B [k,n] only");
-    using Cfg = TpGemmCfg<2, 256>;
-    void (*k)(TpGemmParams) = nullptr;
-    void (*ke)(const TpGemmParams*, int) = nullptr;
-    switch (plan->cfg.variant) {
-      case 1: k = tp_gemm_kernel<2, 256, true, false, false, 1>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 1>; break;
-      case 2: k = tp_gemm_kernel<2, 256, true, false, false, 2>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 2>; break;
-      case 3: k = tp_gemm_kernel<2, 256, true, false, false, 3>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 3>; break;
-      case 4: k = tp_gemm_kernel<2, 256, true, false, false, 4>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 4>; break;
-      case 6: k = tp_gemm_kernel<2, 256, true, false, false, 6>; ke = tp_gemm_emulated_kernel<2, 256, true, false, 6>; break;
-      default: return set_error("unknown variant %d", plan->cfg.variant);
+  if (plan->res.elem == 4) {      // fp32 on kind::tf32, B [n,k]
+    if (plan->res.split) {
+      if (g == 2 && bn == 256) return bind_kernel<2, 256, false, true, true>(plan);
+      if (g == 1 && bn == 128) return bind_kernel<1, 128, false, true, true>(plan);
+      if (g == 2 && bn == 128) return bind_kernel<2, 128, false, true, true>(plan);
+      return set_error("no 3xTF32 kernel for cta_group=%d block_n=%d", g, bn);
     }
-    plan->kernel = k;
-    plan->emu_kernel = ke;
-    for (const void* f : {reinterpret_cast<const void*>(k), reinterpret_cast<const void*>(ke)}) {
-      cudaError_t e = cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
-      if (e != cudaSuccess) { (void)cudaGetLastError(); return set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e)); }
-    }
-    (void)cudaFuncSetAttribute(reinterpret_cast<const void*>(k), cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-    (void)cudaGetLastError();
-    const int fixed = 1024 + kEpiBytes + Cfg::kBarBytes + (plan->res.comm_in_cta == 1 ? kWarpRingBytes : 0);
-    int stages = (227 * 1024 - fixed) / Cfg::kStageBytes;
-    if (stages > Cfg::kStages) stages = Cfg::kStages;
-    plan->stages = stages;
-    plan->smem_bytes = fixed + stages * Cfg::kStageBytes;
-    return 0;
-  }
-  if (plan->res.elem == 4) {      // fp32 through kind::tf32
-    if (g == 1 && bn == 256) return nm ? bind_kernel<1, 256, true, true>(plan) : bind_kernel<1, 256, false, true>(plan);
-    if (g == 2 && bn == 256) return nm ? bind_kernel<2, 256, true, true>(plan) : bind_kernel<2, 256, false, true>(plan);
-    if (g == 1 && bn == 128) return nm ? bind_kernel<1, 128, true, true>(plan) : bind_kernel<1, 128, false, true>(plan);
-    if (g == 2 && bn == 128) return nm ? bind_kernel<2, 128, true, true>(plan) : bind_kernel<2, 128, false, true>(plan);
+    if (g == 1 && bn == 256) return bind_kernel<1, 256, false, true>(plan);
+    if (g == 2 && bn == 256) return bind_kernel<2, 256, false, true>(plan);
+    if (g == 1 && bn == 128) return bind_kernel<1, 128, false, true>(plan);
+    if (g == 2 && bn == 128) return bind_kernel<2, 128, false, true>(plan);
     return set_error("no fp32 kernel for cta_group=%d block_n=%d", g, bn);
   }
   if (g == 1 && bn == 256) return nm ? bind_kernel<1, 256, true>(plan) : bind_kernel<1, 256, false>(plan);
@@ -267,6 +240,8 @@ static void fill_schedule(TpGemmParams& p, const ddlb_tp_gemm_config& c, const R
   p.group_m = r.group_m;
   p.part_rows = r.part_rows;
   p.out_n = static_cast<int>(c.n);
+  p.block_n = r.block_n;
+  p.elem = r.elem;
   if (c.mode == DDLB_MODE_AG_BEFORE || c.mode == DDLB_MODE_RS) {
     p.mblks_per_part = r.part_rows / r.tile_m;
     p.chunk_mblks = r.chunk_rows / r.tile_m;
@@ -274,7 +249,11 @@ static void fill_schedule(TpGemmParams& p, const ddlb_tp_gemm_config& c, const R
     p.mblks_per_part = p.num_m_blocks;
     p.chunk_mblks = p.num_m_blocks;
   }
-  p.rot0 = c.mode == DDLB_MODE_RS ? 1 : 0;
+  p.part0 = r.part0;
+  p.ag_transport = c.ag_transport;
+  p.epi_transport = c.epi_transport;
+  p.rs_transport = c.rs_transport;
+  p.act = c.epilogue_act;
 }
 }  // namespace ddlb
 
@@ -286,7 +265,7 @@ extern "C" int64_t ddlb_tp_gemm_sig_words(const ddlb_tp_gemm_config* cfg) {
   if (cfg->mode == DDLB_MODE_AG_BEFORE) words += static_cast<int64_t>(cfg->world) * (r.part_rows / r.chunk_rows);
   if (cfg->mode == DDLB_MODE_RS) {
     const int64_t nb = (cfg->n + r.block_n - 1) / r.block_n;
-    words += static_cast<int64_t>(cfg->world) * (r.part_rows / ddlb::kBlockM) * nb;
+    words += static_cast<int64_t>(r.part_rows / ddlb::kBlockM) * nb;
   }
   return (words + 63) / 64 * 64;
 }
@@ -295,9 +274,11 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   using namespace ddlb;
   if (cfg == nullptr || out == nullptr) return set_error("null argument");
   *out = nullptr;
+  ddlb_tp_gemm_config normalized = *cfg;
+  if (normalized.world == 1) normalized.mode = DDLB_MODE_PLAIN;   // one rank: nothing to gather or reduce
   Resolved r;
-  if (int rc = resolve(*cfg, r)) return rc;
-  const ddlb_tp_gemm_config& c = *cfg;
+  if (int rc = resolve(normalized, r)) return rc;
+  const ddlb_tp_gemm_config& c = normalized;
   if (c.a == nullptr || c.b == nullptr || c.out[c.rank] == nullptr) return set_error("null a/b/out pointer");
   if (c.world > 1 && c.mode != DDLB_MODE_PLAIN) {
     if (c.sig_local == nullptr) return set_error("sig_local is required for fused modes");
@@ -305,9 +286,15 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
       if (p == c.rank) continue;
       if (c.sig_peer[p] == nullptr) return set_error("sig_peer[%d] is null", p);
       if (c.mode == DDLB_MODE_AG_BEFORE && c.peer_a[p] == nullptr) return set_error("peer_a[%d] is null", p);
-      if (c.mode != DDLB_MODE_AG_BEFORE && c.out[p] == nullptr) return set_error("out[%d] is null", p);
+      if (c.mode == DDLB_MODE_AG_AFTER && c.out[p] == nullptr) return set_error("out[%d] is null", p);
+      if (c.mode == DDLB_MODE_RS && c.stage[p] == nullptr) return set_error("stage[%d] is null", p);
     }
-    if (c.mode == DDLB_MODE_RS && c.stage_local == nullptr) return set_error("stage_local is null");
+    if (c.mode == DDLB_MODE_RS && c.stage[c.rank] == nullptr) return set_error("stage[rank] is null");
+    const bool wants_mc = (c.mode == DDLB_MODE_AG_BEFORE && c.ag_transport == DDLB_AG_PUSH_MULTICAST) ||
+                          (c.mode == DDLB_MODE_AG_AFTER && c.epi_transport == DDLB_EPI_MULTICAST) ||
+                          (c.mode == DDLB_MODE_RS && c.rs_transport == DDLB_RS_PULL_MULTICAST);
+    if (wants_mc && c.mc_ptr == nullptr)
+      return set_error("a multicast transport was selected but mc_ptr is null (no NVLS window)");
   }
 
   auto* plan = new ddlb_tp_gemm_plan();
@@ -341,13 +328,13 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
       rc = make_tmap(&p.tmB, c.b, 2, dims, strides, box, r.elem);
     }
   }
+  // output maps (TMA stores): C of this rank; in AG_AFTER C of every rank. RS stores with
+  // plain 128-bit stores and needs none.
   for (int d = 0; d < c.world && rc == 0; ++d) {
+    if (c.mode == DDLB_MODE_RS) break;
     if (c.out[d] == nullptr) continue;
-    uint64_t rows;
-    if (c.mode == DDLB_MODE_RS) rows = d == c.rank ? r.part_rows : 2ull * c.world * r.part_rows;
-    else rows = static_cast<uint64_t>(c.m);
-    if ((c.mode == DDLB_MODE_PLAIN || c.mode == DDLB_MODE_AG_BEFORE) && d != c.rank) continue;
-    const uint64_t dims[2] = {N, rows};
+    if (c.mode != DDLB_MODE_AG_AFTER && d != c.rank) continue;
+    const uint64_t dims[2] = {N, static_cast<uint64_t>(c.m)};
     const uint64_t strides[1] = {N * E};
     const uint32_t box[2] = {row_elems, 32};
     rc = make_tmap(&p.tmOut[d], c.out[d], 2, dims, strides, box, r.elem);
@@ -356,7 +343,6 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
 
   fill_schedule(p, c, r);
   p.num_k_blocks = (r.kk + static_cast<int>(row_elems) - 1) / static_cast<int>(row_elems);
-  p.n_comm_clusters = r.n_comm_ctas / r.cta_group;
   p.idesc = make_idesc(c.dtype == DDLB_DTYPE_F32 ? 2u : (c.dtype == DDLB_DTYPE_BF16 ? 1u : 0u),
                        static_cast<uint32_t>(r.tile_m),
                        static_cast<uint32_t>(r.block_n), false, c.b_layout == DDLB_B_ROW_MAJOR_KN);
@@ -365,41 +351,46 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   for (int d = 0; d < c.world; ++d) {
     p.peer_a[d] = static_cast<const uint8_t*>(c.peer_a[d]);
     p.sig_peer[d] = c.sig_peer[d];
+    p.stage_base[d] = static_cast<uint8_t*>(c.stage[d]);
+    p.out_raw[d] = static_cast<uint8_t*>(c.out[d]);
   }
   p.peer_a[c.rank] = static_cast<const uint8_t*>(c.a);
   p.chunk_bytes = static_cast<uint32_t>(static_cast<int64_t>(r.chunk_rows) * r.kk * r.elem);
-  p.slice_bytes = r.n_comm_ctas > 0 ? p.chunk_bytes / r.n_comm_ctas : 0;
-  p.comm_push = c.comm_transport == DDLB_COMM_PUSH_CTAS ? 1 : 0;
-  p.comm_in_cta = r.comm_in_cta;
   p.stages = plan->stages;
-  p.stage_local = static_cast<const uint8_t*>(c.stage_local);
-  p.rs_sig_off = kSigChunk;
-  p.rs_tiles_per_src = (r.part_rows / kBlockM) * p.num_n_blocks;
+  p.rs_tiles = (r.part_rows / kBlockM) * p.num_n_blocks;
+  p.mc_ptr = static_cast<uint8_t*>(c.mc_ptr);
   p.sig_local = c.sig_local;
   p.sig_peer[c.rank] = c.sig_local;
   p.trace = static_cast<uint4*>(c.trace);
-  for (int d = 0; d < c.world; ++d) p.out_raw[d] = static_cast<uint8_t*>(c.out[d]);
   *out = plan;
   return 0;
 }
+
+namespace ddlb {
+static void fill_launch(cudaLaunchConfig_t& lc, cudaLaunchAttribute* attr, unsigned grid, int threads,
+                        int smem_bytes, int cta_group, cudaStream_t st) {
+  memset(&lc, 0, sizeof(lc));
+  lc.gridDim = dim3(grid, 1, 1);
+  lc.blockDim = dim3(static_cast<unsigned>(threads), 1, 1);
+  lc.dynamicSmemBytes = static_cast<size_t>(smem_bytes);
+  lc.stream = st;
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = static_cast<unsigned>(cta_group);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  lc.attrs = attr;
+  lc.numAttrs = 1;
+}
+}  // namespace ddlb
 
 extern "C" int ddlb_tp_gemm_run(ddlb_tp_gemm_plan* plan, uint32_t epoch, void* stream) {
   using namespace ddlb;
   if (plan == nullptr) return set_error("null plan");
   plan->params.epoch = epoch;
   cudaLaunchConfig_t lc;
-  memset(&lc, 0, sizeof(lc));
-  lc.gridDim = dim3(static_cast<unsigned>(plan->res.grid), 1, 1);
-  lc.blockDim = dim3(kNumThreads, 1, 1);
-  lc.dynamicSmemBytes = static_cast<size_t>(plan->smem_bytes);
-  lc.stream = static_cast<cudaStream_t>(stream);
   cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = static_cast<unsigned>(plan->res.cta_group);
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  lc.attrs = attr;
-  lc.numAttrs = 1;
+  fill_launch(lc, attr, static_cast<unsigned>(plan->res.grid), plan->res.threads, plan->smem_bytes,
+              plan->res.cta_group, static_cast<cudaStream_t>(stream));
   void* args[1] = {&plan->params};
   cudaError_t e = cudaLaunchKernelExC(&lc, reinterpret_cast<const void*>(plan->kernel), args);
   if (e != cudaSuccess) {
@@ -417,7 +408,7 @@ extern "C" int ddlb_tp_gemm_info(const ddlb_tp_gemm_plan* plan, int32_t out[8]) 
   out[3] = plan->res.cta_group;
   out[4] = plan->res.block_n;
   out[5] = plan->stages;
-  out[6] = plan->res.n_comm_ctas;
+  out[6] = plan->res.threads;
   out[7] = plan->res.chunk_rows;
   return 0;
 }
@@ -437,7 +428,8 @@ extern "C" int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, u
   for (int r = 0; r < world; ++r) {
     if (plans[r] == nullptr) return set_error("null plan %d", r);
     if (plans[r]->emu_kernel == nullptr) return set_error("traced plans cannot be emulated");
-    if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group)
+    if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group ||
+        plans[r]->res.threads != first->res.threads)
       return set_error("emulated ranks must use the same kernel variant");
   }
   int dev = 0, sms = 0;
@@ -447,8 +439,7 @@ extern "C" int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, u
   int clusters_per_rank = (sms / world) / g;
   const int want = first->res.grid / g;            // honour a smaller num_sms request
   if (first->cfg.num_sms > 0 && want < clusters_per_rank) clusters_per_rank = want;
-  if (clusters_per_rank <= first->params.n_comm_clusters)
-    return set_error("%d clusters per emulated rank leave none for the GEMM", clusters_per_rank);
+  if (clusters_per_rank < 1) return set_error("no cluster left per emulated rank");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   TpGemmParams* dparams = nullptr;
   DDLB_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&dparams), sizeof(TpGemmParams) * world, st));
@@ -458,18 +449,9 @@ extern "C" int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, u
                               cudaMemcpyHostToDevice, st));
   }
   cudaLaunchConfig_t lc;
-  memset(&lc, 0, sizeof(lc));
-  lc.gridDim = dim3(static_cast<unsigned>(clusters_per_rank * g * world), 1, 1);
-  lc.blockDim = dim3(kNumThreads, 1, 1);
-  lc.dynamicSmemBytes = static_cast<size_t>(first->smem_bytes);
-  lc.stream = st;
   cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = static_cast<unsigned>(g);
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  lc.attrs = attr;
-  lc.numAttrs = 1;
+  fill_launch(lc, attr, static_cast<unsigned>(clusters_per_rank * g * world), first->res.threads,
+              first->smem_bytes, g, st);
   const TpGemmParams* carg = dparams;
   void* args[2] = {&carg, &clusters_per_rank};
   cudaError_t e = cudaLaunchKernelExC(&lc, reinterpret_cast<const void*>(first->emu_kernel), args);
@@ -538,7 +520,8 @@ extern "C" int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int w
   for (int r = 0; r < world; ++r) {
     if (plans[r] == nullptr) return set_error("null plan %d", r);
     if (plans[r]->emu_kernel == nullptr) return set_error("traced plans cannot be emulated");
-    if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group)
+    if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group ||
+        plans[r]->res.threads != first->res.threads)
       return set_error("emulated ranks must use the same kernel variant");
   }
   int dev = 0, sms = 0;
@@ -548,8 +531,7 @@ extern "C" int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int w
   int clusters_per_rank = (sms / world) / g;
   const int want = first->res.grid / g;
   if (first->cfg.num_sms > 0 && want < clusters_per_rank) clusters_per_rank = want;
-  if (clusters_per_rank <= first->params.n_comm_clusters)
-    return set_error("%d clusters per emulated rank leave none for the GEMM", clusters_per_rank);
+  if (clusters_per_rank < 1) return set_error("no cluster left per emulated rank");
 
   TpGemmParams* dparams = nullptr;
   if (int rc = emulated_scratch_for_current_device(&dparams)) return rc;
@@ -562,18 +544,9 @@ extern "C" int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int w
                               cudaMemcpyHostToDevice, st));
   }
   cudaLaunchConfig_t lc;
-  memset(&lc, 0, sizeof(lc));
-  lc.gridDim = dim3(static_cast<unsigned>(clusters_per_rank * g * world), 1, 1);
-  lc.blockDim = dim3(kNumThreads, 1, 1);
-  lc.dynamicSmemBytes = static_cast<size_t>(first->smem_bytes);
-  lc.stream = st;
   cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = static_cast<unsigned>(g);
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  lc.attrs = attr;
-  lc.numAttrs = 1;
+  fill_launch(lc, attr, static_cast<unsigned>(clusters_per_rank * g * world), first->res.threads,
+              first->smem_bytes, g, st);
   const TpGemmParams* carg = dparams;
   void* args[2] = {&carg, &clusters_per_rank};
   cudaError_t e = cudaLaunchKernelExC(&lc, reinterpret_cast<const void*>(first->emu_kernel), args);
@@ -598,7 +571,7 @@ extern "C" int ddlb_debug_schedule(const ddlb_tp_gemm_config* cfg, int32_t out[1
   fill_schedule(p, *cfg, r);
   out[0] = p.num_m_blocks; out[1] = p.num_n_blocks; out[2] = p.mblks_per_part; out[3] = p.chunk_mblks;
   out[4] = p.group_m; out[5] = r.tile_m; out[6] = r.block_n; out[7] = r.cta_group;
-  out[8] = r.chunk_rows; out[9] = r.n_comm_ctas; out[10] = r.grid; out[11] = r.comm_in_cta;
+  out[8] = r.chunk_rows; out[9] = r.part0; out[10] = r.grid; out[11] = r.threads;
   return 0;
 }
 

@@ -10,13 +10,21 @@
 // (ddlb/primitives/TPColumnwise/pytorch.py:96-102) and cuBLAS GEMM +
 // ncclReduceScatter (ddlb/primitives/TPRowwise/pytorch.py:82-83), and the
 // stream-pipelined nvFuser/TE variants (TPColumnwise/fuser.py:16-146,
-// TPRowwise/fuser.py:15-169): their "algorithm/s/order" knobs are tile orders here.
+// TPRowwise/fuser.py:15-169): their "algorithm/s/order" knobs are tile orders here, their
+// transports (nccl / symmetric-memory copies / multimem) are the data paths below.
 //
-// CTA roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one lane),
-// warp 2 = TMEM allocator, warps 4..7 = epilogue (one TMEM lane quadrant each).
-// In AG_BEFORE the first `n_comm_clusters` clusters do not compute: they pull the
-// peers' row shards over NVLink with bulk-async copies (global -> smem ring -> local
-// global) and publish per-chunk arrival counters that the GEMM producers wait on.
+// CTA roles: warp 0 = TMA producer, warp 1 = MMA issuer (one lane), warp 2 = TMEM allocator,
+// warps 4..7 = epilogue (one TMEM lane quadrant each). Warps 2, 3 and 8..11 ("aux" warps; the
+// last four exist only in launches of 384 threads) carry the collective:
+//   AG_BEFORE  they move A shards over NVLink (128-bit loads/stores through registers, or
+//              multimem.st through the NVSwitch) and publish per-chunk arrival counters that
+//              the TMA producers wait on;
+//   RS         they reduce: every partial tile is stored (by the epilogue warps) into a
+//              staging slot - at the owner (push), or locally (pull) - and the owner's aux
+//              warps sum the d slots of a 32-row x 128-byte unit as soon as all of them have
+//              landed: local loads (push), peer loads (pull) or ONE multimem.ld_reduce per
+//              16 bytes, summed inside the NVSwitch (pull over multicast).
+//   fp32       (3xTF32) warps 8..11 split the fp32 operands into tf32 hi + lo parts.
 //
 // Cross-GPU protocol: all flags are monotonic (value = epoch * arrivals) so
 // back-to-back launches never need a clearing pass; data that can be overwritten by
@@ -30,26 +38,31 @@ namespace ddlb {
 constexpr int kBlockM = 128;   // rows per CTA (a cta_group::2 pair covers 256)
 constexpr int kBlockK = 64;    // 64 x 16-bit = one 128-byte swizzle row
 constexpr int kUmmaK = 16;
-constexpr int kNumThreads = 256;
+constexpr int kBaseThreads = 256;               // warps 0..7
+constexpr int kMaxThreads = 384;                // + aux warps 8..11
 constexpr int kMaxWorld = 8;
-constexpr int kEpiBufBytes = 32 * 128;          // 32 rows x 64 cols x 2 B per warp buffer
+constexpr int kEpiBufBytes = 32 * 128;          // 32 rows x 128 B per warp buffer
 constexpr int kEpiBytes = 4 * 2 * kEpiBufBytes;  // 4 warps x double buffer
 constexpr int kSmemBudget = 193 * 1024;         // operand ring
-constexpr int kCommPiece = 16 * 1024;           // bytes per bulk copy of a comm CTA
-constexpr int kCommRing = 12;
-constexpr int kCommLag = 4;
-constexpr int kWarpPiece = 8 * 1024;         // comm warp in every CTA: piece, ring depth, store lag
-constexpr int kWarpRing = 4;
-constexpr int kWarpLag = 2;
-constexpr int kWarpRingBytes = kWarpRing * kWarpPiece;
 
 enum : int { kModePlain = 0, kModeAGBefore = 1, kModeAGAfter = 2, kModeRS = 3 };
+// who moves the A shards in AG_BEFORE
+enum : int { kAgPull = 0, kAgPush = 1, kAgPushMulticast = 2 };
+// how AG_AFTER's epilogue writes a C tile into every rank's C
+enum : int { kEpiTma = 0, kEpiSt128 = 1, kEpiMulticast = 2 };
+// where RS partial tiles are staged and how the owner sums them
+enum : int { kRsPush = 0, kRsPull = 1, kRsPullMulticast = 2 };
+// activation fused into the epilogue (applied to the fp32 accumulator before rounding)
+enum : int { kActNone = 0, kActRelu = 1, kActSilu = 2, kActGeluTanh = 3 };
 
 // word offsets inside a rank's signal block
 constexpr int kSigReady = 0;    // [src]   epoch written by src when its kernel started
 constexpr int kSigDone = 8;     // [src]   AG_AFTER: += 1 per CTA of src whose stores landed
-constexpr int kSigChunk = 16;   // [chunk] AG_BEFORE: += 1 per comm CTA slice copied
-// RS tile counters follow the chunk flags: [src][cta_tile] += 1 per epilogue warp
+                                //         AG_BEFORE (pull): += 1 per aux warp of src that has
+                                //         finished reading this rank's shard
+constexpr int kSigClaim = 16;   // [2]     RS: reducer work queue heads, by epoch parity
+constexpr int kSigChunk = 32;   // [chunk] AG_BEFORE: += 1 per unit copied;  RS: [cta_tile] += 1
+                                //         per epilogue warp of every rank whose store landed
 
 struct TpGemmParams {
   CUtensorMap tmA;
@@ -63,47 +76,53 @@ struct TpGemmParams {
   int group_m;            // rasterisation: m-blocks per group (L2 reuse)
   int mblks_per_part;     // cluster tiles per rank shard (AG_BEFORE / RS), else num_m_blocks
   int chunk_mblks;        // cluster tiles per chunk (divides mblks_per_part)
-  int rot0;               // 0: own part first (AG), 1: own part last (RS)
-  int n_comm_clusters;    // AG_BEFORE only
+  int part0;              // first shard in visiting order (AG: own; RS push: next rank; else 0)
   int part_rows;          // rows per shard (m / world)
   int out_n;              // N (elements per output row)
+  int block_n;            // BLOCK_N of this kernel (the reducers are not templated on it)
+  int elem;               // bytes per element
   uint32_t idesc;
   uint32_t epoch;
+  int stages;             // operand ring depth actually used (<= Cfg::kStages)
+  int act;                // epilogue activation on the final output (PLAIN / AG_*): kAct*
   // AG_BEFORE
-  const uint8_t* peer_a[kMaxWorld];   // peers' gathered-A buffers (peer mapped)
+  int ag_transport;
+  const uint8_t* peer_a[kMaxWorld];   // every rank's gathered-A buffer (peer mapped)
   uint8_t* local_a;                   // this rank's gathered-A buffer
-  uint32_t chunk_bytes;               // bytes of one chunk (chunk rows * K * 2)
-  uint32_t slice_bytes;               // chunk_bytes / comm CTAs
-  int comm_push;                      // dedicated comm CTAs: 1 = push own shard, 0 = pull peers' shards
-  int comm_in_cta;                    // 1: no dedicated CTAs, warp 3 of EVERY CTA pulls pieces
-  int stages;                         // operand ring depth actually used (<= Cfg::kStages)
+  uint32_t chunk_bytes;               // bytes of one chunk (chunk rows * K * elem)
+  // AG_AFTER
+  int epi_transport;
   // RS
-  const uint8_t* stage_local;         // [2][world][part_rows][N] partials pushed by peers
-  int rs_sig_off;                     // word offset of the RS counters in a signal block
-  int rs_tiles_per_src;               // (part_rows / 128) * num_n_blocks
+  int rs_transport;
+  uint8_t* stage_base[kMaxWorld];     // every rank's staging [2][world][part_rows][N]
+  int rs_tiles;                       // (part_rows / 128) * num_n_blocks counters
+  // multicast alias of: AG_BEFORE the gathered A, AG_AFTER C, RS the staging (or null)
+  uint8_t* mc_ptr;
   // signals
   uint32_t* sig_local;
   uint32_t* sig_peer[kMaxWorld];
   // optional device trace (kTrace kernels only): [cta][role][kTraceSlots] x {tag, arg, time ns}
   uint4* trace;
-  // raw output addresses (same buffers as tmOut[]), used by the register-store push variant
+  // raw output addresses: AG_AFTER every rank's C, otherwise [rank] = this rank's output
   uint8_t* out_raw[kMaxWorld];
 };
 
-template <int kCtaGroup, int kBlockN>
+template <int kCtaGroup, int kBlockN, bool kSplit = false>
 struct TpGemmCfg {
   static constexpr int kTileM = kBlockM * kCtaGroup;
   static constexpr int kLoadN = kBlockN / kCtaGroup;            // B columns staged per CTA
   static constexpr int kStageA = kBlockM * kBlockK * 2;
   static constexpr int kStageB = kLoadN * kBlockK * 2;
-  static constexpr int kStageBytes = kStageA + kStageB;
+  static constexpr int kStageOps = kStageA + kStageB;
+  // 3xTF32: every stage also holds the low-order parts of A and B
+  static constexpr int kStageBytes = kSplit ? 2 * kStageOps : kStageOps;
   static constexpr int kStagesRaw = kSmemBudget / kStageBytes;
   static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
   static constexpr int kTmemCols = 2 * kBlockN;
   static constexpr int kBarBytes = 512;
-  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kEpiBytes + kBarBytes;
+  static constexpr int kFixedBytes = 1024 + kEpiBytes + kBarBytes;
+  static constexpr int kSmemBytes = kFixedBytes + kStages * kStageBytes;
   static_assert(kStages >= 3, "operand ring too shallow");
-  static_assert(kCommRing * kCommPiece <= kStages * kStageBytes, "comm ring does not fit");
   static_assert(kSmemBytes <= 227 * 1024, "shared memory budget exceeded");
 };
 
@@ -138,8 +157,7 @@ __host__ __device__ __forceinline__ TileCoord tile_coord(const TpGemmParams& p, 
   const int rem = ord - stage * per_stage;
   const int pi = rem / p.chunk_mblks;
   const int w = rem - pi * p.chunk_mblks;
-  int part = p.rank + p.rot0 + pi;
-  part = part >= p.world ? part - p.world : part;
+  int part = p.part0 + pi;
   part = part >= p.world ? part - p.world : part;
   c.part = part;
   c.chunk = stage;
@@ -159,317 +177,40 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi, bool bf16) {
   return out;
 }
 
-// v[0..8) hold fp32 bit patterns; add 8 packed 16-bit values to them in fp32.
-__device__ __forceinline__ void add_packed8(uint32_t* v, uint4 raw, bool bf16) {
-  const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float2 f;
-    if (bf16) {
-      __nv_bfloat162 h;
-      memcpy(&h, &w[i], 4);
-      f = __bfloat1622float2(h);
-    } else {
-      __half2 h;
-      memcpy(&h, &w[i], 4);
-      f = __half22float2(h);
-    }
-    v[2 * i] = __float_as_uint(__uint_as_float(v[2 * i]) + f.x);
-    v[2 * i + 1] = __float_as_uint(__uint_as_float(v[2 * i + 1]) + f.y);
+__device__ __forceinline__ float apply_act(float x, int act) {
+  if (act == kActRelu) return fmaxf(x, 0.f);
+  if (act == kActSilu) return x * __frcp_rn(1.f + __expf(-x));
+  // gelu, tanh form: 0.5 x (1 + tanh(sqrt(2/pi) (x + 0.044715 x^3))) = x * sigmoid(2 u)
+  const float u = 0.7978845608f * (x + 0.044715f * x * x * x);
+  return x * __frcp_rn(1.f + __expf(-2.f * u));
+}
+
+__device__ __forceinline__ float2 unpack2(uint32_t w, bool bf16) {
+  if (bf16) {
+    __nv_bfloat162 h;
+    memcpy(&h, &w, 4);
+    return __bfloat1622float2(h);
   }
+  __half2 h;
+  memcpy(&h, &w, 4);
+  return __half22float2(h);
 }
 
 // ---------------------------------------------------------------------------
-// communication CTAs (AG_BEFORE): pull peers' chunks into the local gathered-A
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ void comm_cta_loop(const TpGemmParams& p, uint8_t* ring, uint32_t bar_base,
-                                              int ci, int nci) {
-  // bar_base: kCommRing mbarriers (8 B each), already initialised with count 1
-  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
-  const int n_chunks = chunks_per_part * (p.world - 1);
-  const uint32_t pieces_per_slice = (p.slice_bytes + kCommPiece - 1) / kCommPiece;
-  const int total = n_chunks * static_cast<int>(pieces_per_slice);
-  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
-
-  if (ci == 0 && threadIdx.x < static_cast<unsigned>(p.world) &&
-      static_cast<int>(threadIdx.x) != p.rank) {
-    // tell every peer that this rank's shard is final for this epoch
-    st_release_sys(p.sig_peer[threadIdx.x] + kSigReady + p.rank, p.epoch);
-  }
-  if (threadIdx.x != 0) return;
-
-  uint32_t ready_mask = 1u << p.rank;
-  auto piece_addr = [&](int i, size_t& off, uint32_t& bytes, int& part, int& chunk_in_part,
-                        bool& last) {
-    const int c = i / static_cast<int>(pieces_per_slice);        // chunk in fetch order
-    const uint32_t pc = i - c * pieces_per_slice;
-    const int stage = c / (p.world - 1);
-    const int pi = c - stage * (p.world - 1);
-    int src = p.rank + 1 + pi;
-    src = src >= p.world ? src - p.world : src;
-    part = src;
-    chunk_in_part = stage;
-    const uint32_t in_slice = pc * kCommPiece;
-    bytes = min(static_cast<uint32_t>(kCommPiece), p.slice_bytes - in_slice);
-    off = static_cast<size_t>(src) * part_bytes + static_cast<size_t>(stage) * p.chunk_bytes +
-          static_cast<size_t>(ci) * p.slice_bytes + in_slice;
-    last = (pc + 1 == pieces_per_slice);
-  };
-  auto issue_load = [&](int i) {
-    size_t off; uint32_t bytes; int part, cip; bool last;
-    piece_addr(i, off, bytes, part, cip, last);
-    if (!(ready_mask & (1u << part))) {
-      wait_flag_ge<true>(p.sig_local + kSigReady + part, p.epoch);
-      ready_mask |= 1u << part;
-    }
-    const int slot = i % kCommRing;
-    const uint32_t bar = bar_base + slot * 8;
-    mbar_arrive_expect_tx(bar, bytes);
-    bulk_load(smem_u32(ring + slot * kCommPiece), p.peer_a[part] + off, bytes, bar);
-  };
-
-  const int prefill = total < kCommRing ? total : kCommRing;
-  for (int i = 0; i < prefill; ++i) issue_load(i);
-  // Store pipeline kCommLag groups deep. Group i is piece i's store (an empty group in the
-  // tail), so after committing group i "at most kCommLag pending" means piece i-kCommLag is
-  // in local memory: publish its chunk counter if it closed a chunk, recycle its ring slot.
-  for (int i = 0; i < total + kCommLag; ++i) {
-    if (i < total) {
-      size_t off; uint32_t bytes; int part, cip; bool last;
-      piece_addr(i, off, bytes, part, cip, last);
-      const int slot = i % kCommRing;
-      mbar_wait(bar_base + slot * 8, (i / kCommRing) & 1);
-      bulk_store(p.local_a + off, smem_u32(ring + slot * kCommPiece), bytes);
-    }
-    bulk_commit();
-    const int j = i - kCommLag;
-    if (j >= 0) {
-      bulk_wait<kCommLag>();
-      size_t off; uint32_t bytes; int part, cip; bool last;
-      piece_addr(j, off, bytes, part, cip, last);
-      if (last) {
-        fence_proxy_async();
-        red_add_release_gpu(p.sig_local + kSigChunk + part * chunks_per_part + cip, 1u);
-      }
-      if (j + kCommRing < total) issue_load(j + kCommRing);
-    }
-  }
-  bulk_wait<0>();
-}
-
-// ---------------------------------------------------------------------------
-// communication CTAs (AG_BEFORE, push transport): every rank writes its own shard
-// into all peers' gathered-A buffers. A piece is read ONCE from local memory into
-// shared memory and stored to the d-1 peers from there; remote stores are posted,
-// so a slot is recycled as soon as the stores have read it (short lag) while the
-// chunk counters on the peers are bumped only when the stores have completed
-// (long lag) - neither waits for a round trip on the critical path.
-// ---------------------------------------------------------------------------
-constexpr int kPushReadLag = 3;
-constexpr int kPushDoneLag = 8;
-
-__device__ __forceinline__ void comm_cta_push_loop(const TpGemmParams& p, uint8_t* ring,
-                                                   uint32_t bar_base, int ci, int nci) {
-  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
-  const uint32_t pieces_per_slice = (p.slice_bytes + kCommPiece - 1) / kCommPiece;
-  const int total = chunks_per_part * static_cast<int>(pieces_per_slice);
-  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
-
-  if (ci == 0 && threadIdx.x < static_cast<unsigned>(p.world) &&
-      static_cast<int>(threadIdx.x) != p.rank) {
-    // this rank's previous launch is over: peers may overwrite its gathered buffer
-    st_release_sys(p.sig_peer[threadIdx.x] + kSigReady + p.rank, p.epoch);
-  }
-  if (threadIdx.x != 0) return;
-
-  auto piece_addr = [&](int i, size_t& off, uint32_t& bytes, int& chunk, bool& last) {
-    chunk = i / static_cast<int>(pieces_per_slice);
-    const uint32_t pc = i - chunk * pieces_per_slice;
-    const uint32_t in_slice = pc * kCommPiece;
-    bytes = min(static_cast<uint32_t>(kCommPiece), p.slice_bytes - in_slice);
-    off = static_cast<size_t>(p.rank) * part_bytes + static_cast<size_t>(chunk) * p.chunk_bytes +
-          static_cast<size_t>(ci) * p.slice_bytes + in_slice;
-    last = (pc + 1 == pieces_per_slice);
-  };
-  auto issue_load = [&](int i) {
-    size_t off; uint32_t bytes; int chunk; bool last;
-    piece_addr(i, off, bytes, chunk, last);
-    const int slot = i % kCommRing;
-    const uint32_t bar = bar_base + slot * 8;
-    mbar_arrive_expect_tx(bar, bytes);
-    bulk_load(smem_u32(ring + slot * kCommPiece), p.local_a + off, bytes, bar);
-  };
-
-  const int prefill = total < kCommRing ? total : kCommRing;
-  for (int i = 0; i < prefill; ++i) issue_load(i);
-  for (int d = 1; d < p.world; ++d) {
-    int peer = p.rank + d;
-    peer = peer >= p.world ? peer - p.world : peer;
-    wait_flag_ge<true>(p.sig_local + kSigReady + peer, p.epoch);
-  }
-  for (int i = 0; i < total + kPushDoneLag; ++i) {
-    if (i < total) {
-      size_t off; uint32_t bytes; int chunk; bool last;
-      piece_addr(i, off, bytes, chunk, last);
-      const int slot = i % kCommRing;
-      mbar_wait(bar_base + slot * 8, (i / kCommRing) & 1);
-      const uint32_t src = smem_u32(ring + slot * kCommPiece);
-      for (int d = 1; d < p.world; ++d) {
-        int peer = p.rank + d;
-        peer = peer >= p.world ? peer - p.world : peer;
-        bulk_store(const_cast<uint8_t*>(p.peer_a[peer]) + off, src, bytes);
-      }
-    }
-    bulk_commit();
-    const int jr = i - kPushReadLag;             // stores of piece jr have read their slot
-    if (jr >= 0 && jr + kCommRing < total) {
-      bulk_wait_read<kPushReadLag>();
-      issue_load(jr + kCommRing);
-    }
-    const int jd = i - kPushDoneLag;             // stores of piece jd have completed
-    if (jd >= 0) {
-      size_t off; uint32_t bytes; int chunk; bool last;
-      piece_addr(jd, off, bytes, chunk, last);
-      if (last) {
-        bulk_wait<kPushDoneLag>();
-        fence_proxy_async();
-        for (int d = 1; d < p.world; ++d) {
-          int peer = p.rank + d;
-          peer = peer >= p.world ? peer - p.world : peer;
-          red_add_release_sys(p.sig_peer[peer] + kSigChunk + p.rank * chunks_per_part + chunk, 1u);
-        }
-      }
-    }
-  }
-  bulk_wait<0>();
-}
-
-// ---------------------------------------------------------------------------
-// communication warp in EVERY CTA (AG_BEFORE, default transport). One SM sustains only
-// ~20 GB/s over NVLink whichever way the bytes move, so a handful of dedicated CTAs
-// cannot fill the links; spread over all CTAs the per-SM demand is ~5 GB/s and the
-// GEMM keeps every SM. The pieces (8 KiB) of all chunks, in arrival order, are dealt
-// round-robin to the CTAs; lane 0 of warp 3 pulls its pieces peer -> smem -> local
-// gathered buffer and bumps the chunk's counter once per piece.
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ void comm_warp_loop(const TpGemmParams& p, uint8_t* ring, uint32_t bar_base,
-                                               int ci, int nci) {
-  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
-  const int n_chunks = chunks_per_part * (p.world - 1);
-  const int ppc = static_cast<int>((p.chunk_bytes + kWarpPiece - 1) / kWarpPiece);   // pieces per chunk
-  const int total = n_chunks * ppc;
-  const int n_my = ci < total ? (total - ci + nci - 1) / nci : 0;
-  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
-
-  uint32_t ready_mask = 1u << p.rank;
-  auto piece_addr = [&](int i, size_t& off, uint32_t& bytes, int& part, int& cip) {
-    const int g = ci + i * nci;                    // global piece index
-    const int c = g / ppc;                         // chunk in fetch order (stage-major, peers rotated)
-    const int pc = g - c * ppc;
-    const int stage = c / (p.world - 1);
-    const int pi = c - stage * (p.world - 1);
-    int src = p.rank + 1 + pi;
-    src = src >= p.world ? src - p.world : src;
-    part = src;
-    cip = stage;
-    const uint32_t in_chunk = static_cast<uint32_t>(pc) * kWarpPiece;
-    bytes = min(static_cast<uint32_t>(kWarpPiece), p.chunk_bytes - in_chunk);
-    off = static_cast<size_t>(src) * part_bytes + static_cast<size_t>(stage) * p.chunk_bytes + in_chunk;
-  };
-  auto issue_load = [&](int i) {
-    size_t off; uint32_t bytes; int part, cip;
-    piece_addr(i, off, bytes, part, cip);
-    if (!(ready_mask & (1u << part))) {
-      wait_flag_ge<true>(p.sig_local + kSigReady + part, p.epoch);
-      ready_mask |= 1u << part;
-    }
-    const int slot = i % kWarpRing;
-    const uint32_t bar = bar_base + slot * 8;
-    mbar_arrive_expect_tx(bar, bytes);
-    bulk_load(smem_u32(ring + slot * kWarpPiece), p.peer_a[part] + off, bytes, bar);
-  };
-
-  const int prefill = n_my < kWarpRing ? n_my : kWarpRing;
-  for (int i = 0; i < prefill; ++i) issue_load(i);
-  for (int i = 0; i < n_my + kWarpLag; ++i) {
-    if (i < n_my) {
-      size_t off; uint32_t bytes; int part, cip;
-      piece_addr(i, off, bytes, part, cip);
-      const int slot = i % kWarpRing;
-      mbar_wait(bar_base + slot * 8, (i / kWarpRing) & 1);
-      bulk_store(p.local_a + off, smem_u32(ring + slot * kWarpPiece), bytes);
-    }
-    bulk_commit();
-    const int j = i - kWarpLag;
-    if (j >= 0 && j < n_my) {
-      bulk_wait<kWarpLag>();                       // piece j is in local memory
-      size_t off; uint32_t bytes; int part, cip;
-      piece_addr(j, off, bytes, part, cip);
-      fence_proxy_async();
-      red_add_release_gpu(p.sig_local + kSigChunk + part * chunks_per_part + cip, 1u);
-      if (j + kWarpRing < n_my) issue_load(j + kWarpRing);
-    }
-  }
-  bulk_wait<0>();
-}
-
-// ---------------------------------------------------------------------------
-// communication warps in EVERY CTA, register path (AG_BEFORE, default transport).
-// Measured on B200/NVSwitch: a 128-bit load/store copy moves ~700 GB/s to a peer (both
-// directions busy) while cp.async.bulk through shared memory stays near 400 GB/s. So warps
-// 2 and 3 of every CTA PUSH this rank's shard: each 32 KiB unit is read once from local
-// memory into registers and stored to all d-1 peers' gathered buffers (posted writes),
-// then fenced at system scope and announced with one remote counter bump per peer. No
-// shared memory is used, all SMs keep computing, per-SM NVLink demand is ~5 GB/s.
+// AG_BEFORE: aux warps of EVERY CTA move the A shards (register path).
+// Measured on B200/NVSwitch: a 128-bit load/store copy reaches ~700 GB/s to or from a peer
+// while cp.async.bulk through shared memory stays near 400 GB/s, and a handful of dedicated
+// comm CTAs cannot fill the links (one SM sustains ~20 GB/s over NVLink). Spread over all
+// CTAs the per-SM demand is ~5 GB/s and the GEMM keeps every SM.
+// The shards are cut into 32 KiB units; the units of all chunks, in arrival order, are dealt
+// round-robin to the aux warps of the whole grid.
 // ---------------------------------------------------------------------------
 constexpr int kPushUnit = 32 * 1024;
-constexpr int kPushUnroll = 16;      // 16 x 16 B per lane in flight: 8 KiB per warp
+constexpr int kCopyGroup = 8;                         // 16-byte vectors per lane per group
+constexpr uint32_t kCopyStep = 32 * 16 * kCopyGroup;  // 4 KiB per warp per group
 
-__device__ __forceinline__ void comm_warp_push_regs(const TpGemmParams& p, int gw, int nw, int lane) {
-  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
-  const int upc = static_cast<int>((p.chunk_bytes + kPushUnit - 1) / kPushUnit);   // units per chunk
-  const int total = chunks_per_part * upc;
-  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
-
-  // a peer's gathered buffer may be overwritten once that peer has started this launch
-  if (lane < p.world && lane != p.rank) wait_flag_ge<true>(p.sig_local + kSigReady + lane, p.epoch);
-  __syncwarp();
-
-  for (int u = gw; u < total; u += nw) {
-    const int chunk = u / upc;
-    const uint32_t begin = static_cast<uint32_t>(u - chunk * upc) * kPushUnit;
-    const uint32_t end = min(begin + static_cast<uint32_t>(kPushUnit), p.chunk_bytes);
-    const size_t base = static_cast<size_t>(p.rank) * part_bytes + static_cast<size_t>(chunk) * p.chunk_bytes;
-    for (uint32_t off = begin + lane * 16; off < end; off += 32 * 16 * kPushUnroll) {
-      uint4 v[kPushUnroll];
-#pragma unroll
-      for (int i = 0; i < kPushUnroll; ++i) {
-        const uint32_t o = off + i * 512;
-        if (o < end) v[i] = __ldcs(reinterpret_cast<const uint4*>(p.local_a + base + o));
-      }
-      for (int d = 1; d < p.world; ++d) {
-        int peer = p.rank + d;
-        peer = peer >= p.world ? peer - p.world : peer;
-        uint8_t* dst = const_cast<uint8_t*>(p.peer_a[peer]) + base;
-#pragma unroll
-        for (int i = 0; i < kPushUnroll; ++i) {
-          const uint32_t o = off + i * 512;
-          if (o < end) __stcs(reinterpret_cast<uint4*>(dst + o), v[i]);
-        }
-      }
-    }
-    __threadfence_system();          // this lane's remote stores are performed
-    __syncwarp();
-    if (lane >= 1 && lane < p.world) {
-      int peer = p.rank + lane;
-      peer = peer >= p.world ? peer - p.world : peer;
-      red_add_release_sys(p.sig_peer[peer] + kSigChunk + p.rank * chunks_per_part + chunk, 1u);
-    }
-  }
-}
-
-// One unit of work of a register-path comm warp: `kPushUnit` bytes [begin, end) of chunk
-// `chunk` of rank `src`'s shard; `base` is the byte offset of that chunk in a gathered buffer.
+// One unit of work of a comm warp: `kPushUnit` bytes [begin, end) of chunk `chunk` of rank
+// `src`'s shard; `base` is the byte offset of that chunk in a gathered buffer.
 // Host-callable so the CPU tests can check that the units tile the shards exactly.
 struct CommUnit {
   int src;
@@ -483,8 +224,11 @@ __host__ __device__ __forceinline__ CommUnit pull_unit(const TpGemmParams& p, in
   CommUnit cu;
   const int c = u / upc;                               // chunk in fetch order
   const int stage = c / (p.world - 1);
-  const int pi = c - stage * (p.world - 1);
-  int src = p.rank + 1 + pi;
+  const int f = c - stage * (p.world - 1);             // f-th foreign shard in visiting order
+  int own_at = p.rank - p.part0;                       // position of the own shard in that order
+  own_at = own_at < 0 ? own_at + p.world : own_at;
+  const int pi = f < own_at ? f : f + 1;
+  int src = p.part0 + pi;
   src = src >= p.world ? src - p.world : src;
   cu.src = src;
   cu.chunk = stage;
@@ -495,59 +239,129 @@ __host__ __device__ __forceinline__ CommUnit pull_unit(const TpGemmParams& p, in
   return cu;
 }
 
-// Register-path PULL counterpart of comm_warp_push_regs: the units of all peers' chunks, in
-// arrival order, are dealt round-robin to the comm warps; each is read from the peer's
-// gathered buffer into registers and stored locally, then the local chunk counter is bumped.
-__device__ __forceinline__ void comm_warp_pull_regs(const TpGemmParams& p, int gw, int nw, int lane) {
+// Copy [begin, end) (multiples of 16 bytes) with two register groups in flight: the loads of
+// group i+1 are issued before the stores of group i, so a warp always has 4..8 KiB outstanding
+// (one round trip to a peer is ~2-4 us; the round-1 loop drained between groups and ran the
+// links at ~60 %).
+__device__ __forceinline__ void copy_pipelined(uint8_t* dst, const uint8_t* src, uint32_t begin,
+                                               uint32_t end, int lane) {
+  uint4 va[kCopyGroup], vb[kCopyGroup];
+  const uint32_t l16 = static_cast<uint32_t>(lane) * 16u;
+#define DDLB_LD_GROUP(v, off)                                                          \
+  _Pragma("unroll") for (int i = 0; i < kCopyGroup; ++i) {                             \
+    const uint32_t o = (off) + l16 + static_cast<uint32_t>(i) * 512u;                  \
+    if (o < end) v[i] = __ldcs(reinterpret_cast<const uint4*>(src + o));               \
+  }
+#define DDLB_ST_GROUP(v, off)                                                          \
+  _Pragma("unroll") for (int i = 0; i < kCopyGroup; ++i) {                             \
+    const uint32_t o = (off) + l16 + static_cast<uint32_t>(i) * 512u;                  \
+    if (o < end) __stcg(reinterpret_cast<uint4*>(dst + o), v[i]);                      \
+  }
+  uint32_t off = begin;
+  DDLB_LD_GROUP(va, off)
+  while (off < end) {
+    DDLB_LD_GROUP(vb, off + kCopyStep)
+    DDLB_ST_GROUP(va, off)
+    DDLB_LD_GROUP(va, off + 2 * kCopyStep)
+    DDLB_ST_GROUP(vb, off + kCopyStep)
+    off += 2 * kCopyStep;
+  }
+#undef DDLB_LD_GROUP
+#undef DDLB_ST_GROUP
+}
+
+// PULL (default): every unit of every peer's shard is read from the peer's buffer into
+// registers and stored locally, then the local chunk counter is bumped. At the end each warp
+// tells every peer that it will not read that peer's shard again in this launch.
+__device__ __forceinline__ void comm_warp_pull(const TpGemmParams& p, int gw, int nw, int lane) {
   const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
   const int upc = static_cast<int>((p.chunk_bytes + kPushUnit - 1) / kPushUnit);
   const int total = chunks_per_part * (p.world - 1) * upc;
   const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
 
+  // a peer's shard is final once that peer has started this launch
   if (lane < p.world && lane != p.rank) wait_flag_ge<true>(p.sig_local + kSigReady + lane, p.epoch);
   __syncwarp();
 
   for (int u = gw; u < total; u += nw) {
     const CommUnit cu = pull_unit(p, u, upc, part_bytes);
-    const int src = cu.src;
-    const int stage = cu.chunk;
-    const uint32_t begin = cu.begin;
-    const uint32_t end = cu.end;
-    const size_t base = cu.base;
-    const uint8_t* from = p.peer_a[src] + base;
-    for (uint32_t off = begin + lane * 16; off < end; off += 32 * 16 * kPushUnroll) {
-      uint4 v[kPushUnroll];
-#pragma unroll
-      for (int i = 0; i < kPushUnroll; ++i) {
-        const uint32_t o = off + i * 512;
-        if (o < end) v[i] = __ldcs(reinterpret_cast<const uint4*>(from + o));
-      }
-#pragma unroll
-      for (int i = 0; i < kPushUnroll; ++i) {
-        const uint32_t o = off + i * 512;
-        if (o < end) __stcg(reinterpret_cast<uint4*>(p.local_a + base + o), v[i]);
-      }
-    }
+    copy_pipelined(p.local_a + cu.base, p.peer_a[cu.src] + cu.base, cu.begin, cu.end, lane);
     __threadfence();
     __syncwarp();
     if (lane == 0)
-      red_add_release_gpu(p.sig_local + kSigChunk + src * chunks_per_part + stage, 1u);
+      red_add_release_gpu(p.sig_local + kSigChunk + cu.src * chunks_per_part + cu.chunk, 1u);
+  }
+  __syncwarp();
+  if (lane < p.world && lane != p.rank)
+    red_add_release_sys(p.sig_peer[lane] + kSigDone + p.rank, 1u);
+}
+
+// PUSH: every unit of the own shard is read once from local memory and stored to all d-1
+// peers' gathered buffers (posted writes), fenced at system scope and announced with one
+// remote counter bump per peer. kMulticast: ONE multimem.st per 16 bytes instead, replicated
+// to every rank by the NVSwitch (egress 1x instead of (d-1)x).
+template <bool kMulticast>
+__device__ __forceinline__ void comm_warp_push(const TpGemmParams& p, int gw, int nw, int lane) {
+  const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
+  const int upc = static_cast<int>((p.chunk_bytes + kPushUnit - 1) / kPushUnit);
+  const int total = chunks_per_part * upc;
+  const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
+
+  // a peer's gathered buffer may be overwritten once that peer has started this launch
+  if (lane < p.world && lane != p.rank) wait_flag_ge<true>(p.sig_local + kSigReady + lane, p.epoch);
+  __syncwarp();
+
+  for (int u = gw; u < total; u += nw) {
+    const int chunk = u / upc;
+    const uint32_t begin = static_cast<uint32_t>(u - chunk * upc) * kPushUnit;
+    const uint32_t end = min(begin + static_cast<uint32_t>(kPushUnit), p.chunk_bytes);
+    const size_t base = static_cast<size_t>(p.rank) * part_bytes + static_cast<size_t>(chunk) * p.chunk_bytes;
+    for (uint32_t off = begin + lane * 16; off < end; off += kCopyStep * 2) {
+      uint4 v[2 * kCopyGroup];
+#pragma unroll
+      for (int i = 0; i < 2 * kCopyGroup; ++i) {
+        const uint32_t o = off + i * 512;
+        if (o < end) v[i] = __ldcs(reinterpret_cast<const uint4*>(p.local_a + base + o));
+      }
+      if constexpr (kMulticast) {
+#pragma unroll
+        for (int i = 0; i < 2 * kCopyGroup; ++i) {
+          const uint32_t o = off + i * 512;
+          if (o < end) multimem_st_v4(p.mc_ptr + base + o, v[i]);
+        }
+      } else {
+        for (int d = 1; d < p.world; ++d) {
+          int peer = p.rank + d;
+          peer = peer >= p.world ? peer - p.world : peer;
+          uint8_t* dst = const_cast<uint8_t*>(p.peer_a[peer]) + base;
+#pragma unroll
+          for (int i = 0; i < 2 * kCopyGroup; ++i) {
+            const uint32_t o = off + i * 512;
+            if (o < end) __stcs(reinterpret_cast<uint4*>(dst + o), v[i]);
+          }
+        }
+      }
+    }
+    __threadfence_system();          // this lane's remote stores are performed
+    __syncwarp();
+    if (lane >= 1 && lane < p.world) {
+      int peer = p.rank + lane;
+      peer = peer >= p.world ? peer - p.world : peer;
+      red_add_release_sys(p.sig_peer[peer] + kSigChunk + p.rank * chunks_per_part + chunk, 1u);
+    }
   }
 }
 
-// ---------------------------------------------------------------------------
-// the kernel
-// ---------------------------------------------------------------------------
 // ---------------------------------------------------------------------------
 // Opt-in device trace: a timeline of one launch without a profiler (ncu cannot replay
 // kernels that wait for other ranks). Compiled in only for kTrace instantiations, so the
 // production kernels carry no trace code at all.
 // ---------------------------------------------------------------------------
 constexpr int kTraceSlots = 128;
-constexpr int kTraceRoles = 4;   // 0 producer, 1 mma, 2 epilogue (warp 4), 3 comm (warp 2)
+constexpr int kTraceRoles = 4;   // 0 producer, 1 mma, 2 epilogue (warp 4), 3 aux (warp 2)
 enum : uint32_t {
   kEvStart = 1, kEvTileBegin = 2, kEvFlagWaited = 3, kEvTileIssued = 4, kEvAccReady = 5,
-  kEvOwnWaited = 6, kEvTileStored = 7, kEvCommUnit = 8, kEvEnd = 9,
+  kEvUnitReady = 6, kEvTileStored = 7, kEvUnitDone = 8, kEvEnd = 9,
 };
 
 template <bool kTrace>
@@ -556,7 +370,7 @@ struct Tracer {
   int n;
   __device__ __forceinline__ Tracer(const TpGemmParams& p, int cta, int role) : base(nullptr), n(0) {
     if constexpr (kTrace) {
-      if (p.trace != nullptr)
+      if (p.trace != nullptr && cta >= 0)
         base = p.trace + (static_cast<size_t>(cta) * kTraceRoles + role) * kTraceSlots;
     }
   }
@@ -571,11 +385,12 @@ struct Tracer {
 };
 
 // Store one staged epilogue chunk (32 rows x 128 bytes, 128-byte swizzled in shared memory)
-// with 128-bit stores: per instruction the warp writes 4 rows x 128 contiguous bytes. Used by
-// the push variant for PEER destinations, where plain stores move ~690 GB/s over NVLink and
-// TMA stores were measured at ~400-530 GB/s.
+// with 128-bit stores: per instruction the warp writes 4 rows x 128 contiguous bytes. Plain
+// stores move ~690 GB/s to a peer over NVLink; TMA stores were measured at ~400-530 GB/s.
+// kMulticast: multimem.st, one store reaches every rank's copy.
+template <bool kMulticast>
 __device__ __forceinline__ void store_chunk_st128(uint8_t* dst_base, size_t pitch_bytes, int row0,
-                                                  int col_byte0, int row_limit, int col_limit_bytes,
+                                                  int col_byte0, int col_limit_bytes,
                                                   uint32_t sbase, int lane) {
 #pragma unroll
   for (int it = 0; it < 8; ++it) {
@@ -588,66 +403,184 @@ __device__ __forceinline__ void store_chunk_st128(uint8_t* dst_base, size_t pitc
                  : "r"(src)
                  : "memory");
     const int colb = col_byte0 + j * 16;
-    if (row0 + r < row_limit && colb < col_limit_bytes) {
-      uint4* dst = reinterpret_cast<uint4*>(dst_base + static_cast<size_t>(row0 + r) * pitch_bytes + colb);
-      asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(v.x), "r"(v.y), "r"(v.z),
-                   "r"(v.w)
-                   : "memory");
+    if (colb < col_limit_bytes) {
+      uint8_t* dst = dst_base + static_cast<size_t>(row0 + r) * pitch_bytes + colb;
+      if constexpr (kMulticast) multimem_st_v4(dst, v);
+      else st_global_v4(dst, v);
     }
   }
 }
 
-// kF32: fp32 inputs and outputs through kind::tf32 (operands are read as TF32 by the tensor
-// core, fp32 accumulation). A 128-byte swizzle row then holds 32 elements and one MMA covers
-// 8 of them, so the byte geometry of the operand ring is identical to the 16-bit case.
-// kVariant: experimental schedule variants compiled as separate instantiations (bit 0: RS
-// announces a pushed tile as soon as its stores have completed instead of at the next tile;
-// bit 1: RS own-tile epilogue issues the staged-partial loads of two sources before adding;
-// bit 2: tiles pushed to PEERS (RS, AG_AFTER) are written with 128-bit stores from the staged
-// shared-memory rows instead of TMA stores).
-template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kTrace = false,
-          int kVariant = 0>
+// ---------------------------------------------------------------------------
+// RS: the reducers. The own shard [part_rows, N] is cut into units of 32 rows x 128 bytes
+// (the epilogue's staging granule). Unit u belongs to counter tile u / units_per_tile; a
+// unit is ready when all 4 epilogue warps of all d ranks have announced that tile. Warps
+// claim units from a queue head in the signal block (one head per epoch parity; the other
+// one is reset for the next launch).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, bool bf16) {
+  const uint32_t parity = p.epoch & 1u;
+  const int segs = p.block_n * p.elem / 128;            // 128-byte column segments per n-block
+  const int units_per_tile = 4 * segs;
+  const int total = p.rs_tiles * units_per_tile;
+  const size_t pitch = static_cast<size_t>(p.out_n) * p.elem;
+  const size_t slot_bytes = static_cast<size_t>(p.part_rows) * pitch;
+  const uint32_t target = 4u * static_cast<uint32_t>(p.world) * p.epoch;
+  uint32_t* head = p.sig_local + kSigClaim + parity;
+  const int r_in = lane >> 3, j = lane & 7;
+  uint8_t* out = p.out_raw[p.rank];
+
+  while (true) {
+    int u = 0;
+    if (lane == 0) u = static_cast<int>(atomicAdd(head, 1u));
+    u = __shfl_sync(0xffffffffu, u, 0);
+    if (u >= total) break;
+    const int tile = u / units_per_tile;
+    const int sub = u - tile * units_per_tile;
+    const int q = sub / segs, c = sub - q * segs;
+    const int rb = tile / p.num_n_blocks, nb = tile - rb * p.num_n_blocks;
+    const int row0 = rb * kBlockM + q * 32;
+    const int colb = (nb * p.block_n) * p.elem + c * 128 + j * 16;
+    if (lane == 0) wait_flag_ge<true>(p.sig_local + kSigChunk + tile, target);
+    __syncwarp();
+    const bool active = colb < static_cast<int>(pitch);   // n-blocks may overhang N
+
+    if (!active) {
+      // nothing in this 16-byte column for this lane; stay converged for the next claim
+    } else if (p.rs_transport == kRsPullMulticast) {
+      // one load per 16 bytes returns the sum over all ranks, added in the NVSwitch
+      const uint8_t* src = p.mc_ptr + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes;
+      uint4 v[8];
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const size_t o = static_cast<size_t>(row0 + it * 4 + r_in) * pitch + colb;
+        if (p.elem == 4) v[it] = multimem_ld_reduce_f32x4(src + o);
+        else if (bf16) v[it] = multimem_ld_reduce_bf16x8(src + o);
+        else v[it] = multimem_ld_reduce_f16x8(src + o);
+      }
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const size_t o = static_cast<size_t>(row0 + it * 4 + r_in) * pitch + colb;
+        st_global_v4(out + o, v[it]);
+      }
+    } else {
+    // push: the d partials sit in the local staging slots [parity][src];
+    // pull: in slot [parity][rank] of every rank's staging (peer loads)
+    const bool pull = p.rs_transport == kRsPull;
+#pragma unroll 1
+    for (int it0 = 0; it0 < 8; it0 += 2) {
+      uint4 raw[kMaxWorld][2];
+#pragma unroll
+      for (int s = 0; s < kMaxWorld; ++s) {
+        if (s < p.world) {
+          const uint8_t* src = pull
+              ? p.stage_base[s] + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes
+              : p.stage_base[p.rank] + (static_cast<size_t>(parity) * p.world + s) * slot_bytes;
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            const size_t o = static_cast<size_t>(row0 + (it0 + t) * 4 + r_in) * pitch + colb;
+            raw[s][t] = __ldcg(reinterpret_cast<const uint4*>(src + o));
+          }
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        uint4 res;
+        if (p.elem == 4) {
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int s = 0; s < kMaxWorld; ++s) {
+            if (s < p.world) {
+              acc.x += __uint_as_float(raw[s][t].x);
+              acc.y += __uint_as_float(raw[s][t].y);
+              acc.z += __uint_as_float(raw[s][t].z);
+              acc.w += __uint_as_float(raw[s][t].w);
+            }
+          }
+          res = make_uint4(__float_as_uint(acc.x), __float_as_uint(acc.y), __float_as_uint(acc.z),
+                           __float_as_uint(acc.w));
+        } else {
+          float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int s = 0; s < kMaxWorld; ++s) {
+            if (s < p.world) {
+              const uint32_t w[4] = {raw[s][t].x, raw[s][t].y, raw[s][t].z, raw[s][t].w};
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float2 f = unpack2(w[i], bf16);
+                acc[2 * i] += f.x;
+                acc[2 * i + 1] += f.y;
+              }
+            }
+          }
+          res = make_uint4(pack2(acc[0], acc[1], bf16), pack2(acc[2], acc[3], bf16),
+                           pack2(acc[4], acc[5], bf16), pack2(acc[6], acc[7], bf16));
+        }
+        const size_t o = static_cast<size_t>(row0 + (it0 + t) * 4 + r_in) * pitch + colb;
+        st_global_v4(out + o, res);
+      }
+    }
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// the kernel
+// ---------------------------------------------------------------------------
+// kF32: fp32 inputs and outputs through kind::tf32. A 128-byte swizzle row then holds 32
+// elements and one MMA covers 8 of them, so the byte geometry of the operand ring is
+// identical to the 16-bit case. kSplit (with kF32): 3xTF32 - warps 8..11 write the low-order
+// parts lo = x - tf32(x) of both operand tiles next to them and the issuer runs three MMAs
+// per k-step (hi*hi + hi*lo + lo*hi), which restores ~fp32 accuracy
+// (BASELINE.json north star; the reference's default dtype is float32,
+// ddlb/primitives/TPColumnwise/tp_columnwise.py:32).
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kSplit = false,
+          bool kTrace = false>
 __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cluster,
                                              const int nclusters) {
-  using Cfg = TpGemmCfg<kCtaGroup, kBlockN>;
+  using Cfg = TpGemmCfg<kCtaGroup, kBlockN, kSplit>;
+  static_assert(!kSplit || kF32, "the hi/lo split exists for fp32 only");
   constexpr int kElem = kF32 ? 4 : 2;                 // bytes per element
   constexpr int kRowElems = 128 / kElem;              // elements per 128-byte swizzle row
   constexpr int kKPerStage = kRowElems;               // k elements per pipeline stage
   constexpr int kKPerMma = 32 / kElem;                // 16 (f16/bf16) or 8 (tf32)
-  const int kStages = p.stages;                               // runtime ring depth
-  const bool comm_in_cta = p.mode == kModeAGBefore && p.comm_in_cta == 1;   // TMA pull ring in warp 3
-  const bool comm_regs = p.mode == kModeAGBefore && p.comm_in_cta >= 2;     // register path, warps 2+3
-  const bool comm_regs_pull = p.comm_in_cta == 3;
+  const int kStages = p.stages;                       // runtime ring depth
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~static_cast<uintptr_t>(1023));
-  uint8_t* smem_ops = smem;                                   // [stage]{A, B}
+  uint8_t* smem_ops = smem;                                   // [stage]{A, B[, A_lo, B_lo]}
   uint8_t* smem_epi = smem + kStages * Cfg::kStageBytes;      // [warp][2][4 KB]
-  uint8_t* smem_comm = smem_epi + kEpiBytes;                  // comm warp ring (comm_in_cta only)
-  uint8_t* smem_bar = smem_comm + (comm_in_cta ? kWarpRingBytes : 0);
-  const uint32_t bar_full = smem_u32(smem_bar);               // [kStages] (also comm ring, <= 12)
-  const uint32_t bar_empty = bar_full + 12 * 8;               // [kStages]
-  const uint32_t bar_tfull = bar_empty + 12 * 8;              // [2]
+  uint8_t* smem_bar = smem_epi + kEpiBytes;
+  const uint32_t bar_full = smem_u32(smem_bar);               // [kStages] TMA landed
+  const uint32_t bar_empty = bar_full + 8 * 8;                // [kStages] MMAs retired
+  const uint32_t bar_split = bar_empty + 8 * 8;               // [kStages] lo parts written (kSplit)
+  const uint32_t bar_tfull = bar_split + 8 * 8;               // [2]
   const uint32_t bar_tempty = bar_tfull + 2 * 8;              // [2]
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(smem_bar + 28 * 8);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const int nwarps = static_cast<int>(blockDim.x >> 5);
+  const int n_aux = 2 + (nwarps - 8);                         // warps 2, 3, 8..
+  const int aux = warp == 2 ? 0 : warp == 3 ? 1 : warp >= 8 ? warp - 6 : -1;
   const uint32_t cta_rank = kCtaGroup == 2 ? cluster_ctarank() : 0u;
-  const bool is_comm = (p.mode == kModeAGBefore) && cluster < p.n_comm_clusters;
+  const int cta = cluster * kCtaGroup + static_cast<int>(cta_rank);
+  const int nctas = nclusters * kCtaGroup;
   const bool bf16 = ((p.idesc >> 7) & 7u) == 1u;
 
   // ------------------------------------------------------------------ setup
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&p.tmA);
     prefetch_tmap(&p.tmB);
-    prefetch_tmap(&p.tmOut[p.rank]);
+    if (p.mode != kModeRS) prefetch_tmap(&p.tmOut[p.rank]);   // RS stores without TMA
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < 12; ++s) {
+    for (int s = 0; s < 8; ++s) {
       mbar_init(bar_full + s * 8, 1);
       mbar_init(bar_empty + s * 8, 1);
+      mbar_init(bar_split + s * 8, 4 * kCtaGroup);            // one arrival per split warp
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(bar_tfull + a * 8, 1);
@@ -666,39 +599,23 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
   const uint32_t tmem_base = *tmem_ptr_smem;
 
   const int num_tiles = p.num_m_blocks * p.num_n_blocks;
-  const int gemm_cluster = cluster - (p.mode == kModeAGBefore ? p.n_comm_clusters : 0);
-  const int gemm_clusters = nclusters - (p.mode == kModeAGBefore ? p.n_comm_clusters : 0);
 
-  if (is_comm) {
-    // -------------------------------------------------------- comm role
-    if (p.comm_push)
-      comm_cta_push_loop(p, smem_ops, bar_full, cluster * kCtaGroup + static_cast<int>(cta_rank),
-                         p.n_comm_clusters * kCtaGroup);
-    else
-      comm_cta_loop(p, smem_ops, bar_full, cluster * kCtaGroup + static_cast<int>(cta_rank),
-                    p.n_comm_clusters * kCtaGroup);
-  } else if (warp == 0 && lane == 0) {
+  if (warp == 0 && lane == 0) {
     // -------------------------------------------------------- TMA producer
     const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
-    const uint32_t chunk_target =
-        p.epoch * (comm_regs ? (p.chunk_bytes + kPushUnit - 1) / kPushUnit
-                   : comm_in_cta ? (p.chunk_bytes + kWarpPiece - 1) / kWarpPiece
-                                 : static_cast<uint32_t>(p.n_comm_clusters * kCtaGroup));
+    const uint32_t chunk_target = p.epoch * ((p.chunk_bytes + kPushUnit - 1) / kPushUnit);
     const uint32_t full_leader = kCtaGroup == 2 ? mapa(bar_full, 0) : bar_full;
     int stage = 0;
     uint32_t phase = 0;
-    Tracer<kTrace> tr(p, cluster * kCtaGroup + static_cast<int>(cta_rank), 0);
+    Tracer<kTrace> tr(p, cta, 0);
     tr.ev(kEvStart, 0);
-    for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
+    for (int t = cluster; t < num_tiles; t += nclusters) {
       const TileCoord tc = tile_coord(p, t);
       tr.ev(kEvTileBegin, static_cast<uint32_t>(t));
       if (p.mode == kModeAGBefore && tc.part != p.rank) {
-        if (p.comm_push || (comm_regs && !comm_regs_pull))   // counter bumped over NVLink
-          wait_flag_ge<true>(p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk,
-                             chunk_target);
-        else
-          wait_flag_ge<false>(p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk,
-                              chunk_target);
+        const uint32_t* flag = p.sig_local + kSigChunk + tc.part * chunks_per_part + tc.chunk;
+        if (p.ag_transport == kAgPull) wait_flag_ge<false>(flag, chunk_target);
+        else wait_flag_ge<true>(flag, chunk_target);       // counter bumped over NVLink
         fence_proxy_async();      // flag acquired by the generic proxy, data read by TMA
         tr.ev(kEvFlagWaited, static_cast<uint32_t>(t));
       }
@@ -708,9 +625,13 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         mbar_wait(bar_empty + stage * 8, phase ^ 1u);
         uint8_t* sa = smem_ops + stage * Cfg::kStageBytes;
         uint8_t* sb = sa + Cfg::kStageA;
-        if (kCtaGroup == 1 || cta_rank == 0)
-          mbar_arrive_expect_tx(bar_full + stage * 8, Cfg::kStageBytes * kCtaGroup);
-        const uint32_t fb = full_leader + stage * 8;
+        // 3xTF32: each CTA watches its own half land (its split warps transform it); the
+        // issuer then waits for the split barrier only. Otherwise both halves signal the
+        // leader's barrier.
+        if constexpr (kSplit) mbar_arrive_expect_tx(bar_full + stage * 8, Cfg::kStageOps);
+        else if (kCtaGroup == 1 || cta_rank == 0)
+          mbar_arrive_expect_tx(bar_full + stage * 8, Cfg::kStageOps * kCtaGroup);
+        const uint32_t fb = (kSplit ? bar_full : full_leader) + stage * 8;
         tma_load_2d<kCtaGroup>(smem_u32(sa), &p.tmA, fb, kb * kKPerStage, m0);
         if constexpr (kBNMajor)
           tma_load_3d<kCtaGroup>(smem_u32(sb), &p.tmB, fb, 0, kb * kKPerStage, n0 / kRowElems);
@@ -719,20 +640,6 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
-  } else if ((warp == 2 || warp == 3) && comm_regs) {
-    // -------------------------------------------------------- comm warps (every CTA, registers)
-    const int ci = cluster * kCtaGroup + static_cast<int>(cta_rank);
-    if (ci == 0 && warp == 3 && lane < p.world && lane != p.rank)
-      st_release_sys(p.sig_peer[lane] + kSigReady + p.rank, p.epoch);   // my previous launch is over
-    if (comm_regs_pull) comm_warp_pull_regs(p, ci * 2 + (warp - 2), nclusters * kCtaGroup * 2, lane);
-    else comm_warp_push_regs(p, ci * 2 + (warp - 2), nclusters * kCtaGroup * 2, lane);
-  } else if (warp == 3 && comm_in_cta) {
-    // -------------------------------------------------------- comm warp (every CTA)
-    const int ci = cluster * kCtaGroup + static_cast<int>(cta_rank);
-    if (ci == 0 && lane < p.world && lane != p.rank)
-      st_release_sys(p.sig_peer[lane] + kSigReady + p.rank, p.epoch);   // my shard is final
-    if (lane == 0)
-      comm_warp_loop(p, smem_comm, bar_full + 8 * 8, ci, nclusters * kCtaGroup);
   } else if (warp == 1 && lane == 0 && cta_rank == 0) {
     // -------------------------------------------------------- MMA issuer
     // K-major operand: 8-row groups 1024 B apart, k-step = 32 B inside the swizzle row.
@@ -744,27 +651,32 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     uint32_t phase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    Tracer<kTrace> tr(p, cluster * kCtaGroup + static_cast<int>(cta_rank), 1);
-    for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
+    Tracer<kTrace> tr(p, cta, 1);
+    for (int t = cluster; t < num_tiles; t += nclusters) {
       mbar_wait(bar_tempty + acc * 8, acc_phase ^ 1u);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kBlockN);
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
-        mbar_wait(bar_full + stage * 8, phase);
+        if constexpr (kSplit) mbar_wait(bar_split + stage * 8, phase);   // implies both halves landed
+        else mbar_wait(bar_full + stage * 8, phase);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem_ops + stage * Cfg::kStageBytes);
         const uint64_t adesc = make_smem_desc_sw128(sa, 16, 1024);
         const uint64_t bdesc = make_smem_desc_sw128(sa + Cfg::kStageA, kBLbo, 1024);
 #pragma unroll
         for (int k = 0; k < kKPerStage / kKPerMma; ++k) {
-          if constexpr (kF32)
-            umma_tf32<kCtaGroup>(tmem_d, adesc + static_cast<uint64_t>(k * (32 >> 4)),
-                                 bdesc + static_cast<uint64_t>(k * kBStep), p.idesc,
-                                 static_cast<uint32_t>((kb | k) != 0));
-          else
-            umma_f16<kCtaGroup>(tmem_d, adesc + static_cast<uint64_t>(k * (32 >> 4)),
-                                bdesc + static_cast<uint64_t>(k * kBStep), p.idesc,
-                                static_cast<uint32_t>((kb | k) != 0));
+          const uint64_t ak = adesc + static_cast<uint64_t>(k * (32 >> 4));
+          const uint64_t bk = bdesc + static_cast<uint64_t>(k * kBStep);
+          if constexpr (kF32) {
+            umma_tf32<kCtaGroup>(tmem_d, ak, bk, p.idesc, static_cast<uint32_t>((kb | k) != 0));
+            if constexpr (kSplit) {
+              constexpr uint64_t kLo = static_cast<uint64_t>(Cfg::kStageOps >> 4);
+              umma_tf32<kCtaGroup>(tmem_d, ak, bk + kLo, p.idesc, 1u);   // hi(A) * lo(B)
+              umma_tf32<kCtaGroup>(tmem_d, ak + kLo, bk, p.idesc, 1u);   // lo(A) * hi(B)
+            }
+          } else {
+            umma_f16<kCtaGroup>(tmem_d, ak, bk, p.idesc, static_cast<uint32_t>((kb | k) != 0));
+          }
         }
         umma_commit<kCtaGroup>(bar_empty + stage * 8);     // smem slot reusable when MMAs retire
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
@@ -773,7 +685,65 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
       tr.ev(kEvTileIssued, static_cast<uint32_t>(t));
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
-  } else if (warp >= 4) {
+  } else if (kSplit && warp >= 8) {
+    // -------------------------------------------------------- 3xTF32 split warps
+    // The tensor core reads the upper 19 bits of an fp32 operand. lo = x - that value is
+    // exact in fp32 and itself fits a tf32 mantissa to ~2^-21 relative to x. The lo tiles use
+    // the same swizzled byte positions as the hi tiles, so the transform is elementwise.
+    if constexpr (kSplit) {
+      const int sw = warp - 8;                               // 0..3
+      const uint32_t split_leader = kCtaGroup == 2 ? mapa(bar_split, 0) : bar_split;
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = cluster; t < num_tiles; t += nclusters) {
+        for (int kb = 0; kb < p.num_k_blocks; ++kb) {
+          mbar_wait(bar_full + stage * 8, phase);            // this CTA's half has landed
+          uint8_t* base = smem_ops + stage * Cfg::kStageBytes;
+          constexpr int kVecs = Cfg::kStageOps / 16;         // 16-byte vectors in A + B
+          for (int v = sw * 32 + lane; v < kVecs; v += 128) {
+            float4 x = *reinterpret_cast<const float4*>(base + v * 16);
+            float4 lo;
+            lo.x = x.x - __uint_as_float(__float_as_uint(x.x) & 0xffffe000u);
+            lo.y = x.y - __uint_as_float(__float_as_uint(x.y) & 0xffffe000u);
+            lo.z = x.z - __uint_as_float(__float_as_uint(x.z) & 0xffffe000u);
+            lo.w = x.w - __uint_as_float(__float_as_uint(x.w) & 0xffffe000u);
+            *reinterpret_cast<float4*>(base + Cfg::kStageOps + v * 16) = lo;
+          }
+          fence_proxy_async_smem();                          // generic writes -> tensor-core reads
+          __syncwarp();
+          if (lane == 0) {
+            if (kCtaGroup == 2 && cta_rank != 0) mbar_arrive_cluster(split_leader + stage * 8);
+            else mbar_arrive(bar_split + stage * 8);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (aux >= 0 && p.mode == kModeAGBefore && p.world > 1) {
+    // -------------------------------------------------------- comm warps (every CTA)
+    if (cta == 0 && aux == 1 && lane < p.world && lane != p.rank)
+      st_release_sys(p.sig_peer[lane] + kSigReady + p.rank, p.epoch);   // my previous launch is over
+    const int na = kSplit ? 2 : n_aux;                       // warps 8.. split operands in 3xTF32
+    if (aux < na) {
+      Tracer<kTrace> tr(p, (warp == 2 && lane == 0) ? cta : -1, 3);
+      tr.ev(kEvStart, 0);
+      const int gw = cta * na + aux, nw = nctas * na;
+      if (p.ag_transport == kAgPull) comm_warp_pull(p, gw, nw, lane);
+      else if (p.ag_transport == kAgPushMulticast) comm_warp_push<true>(p, gw, nw, lane);
+      else comm_warp_push<false>(p, gw, nw, lane);
+      tr.ev(kEvEnd, 0);
+      if (p.ag_transport == kAgPull && cta == 0 && aux == 0) {
+        // every peer has finished reading this rank's shard: the caller may overwrite it as
+        // soon as this kernel is complete (same guarantee as ncclAllGather's send buffer)
+        if (lane < p.world && lane != p.rank)
+          wait_flag_ge<true>(p.sig_local + kSigDone + lane, p.epoch * static_cast<uint32_t>(nw));
+      }
+    }
+  } else if (aux >= 0 && p.mode == kModeRS && !(kSplit && warp >= 8)) {
+    // -------------------------------------------------------- reducers (every CTA)
+    if (cta == 0 && aux == 0 && lane == 0) p.sig_local[kSigClaim + ((p.epoch & 1u) ^ 1u)] = 0u;
+    rs_reduce_loop(p, lane, bf16);
+  } else if (warp >= 4 && warp < 8) {
     // -------------------------------------------------------- epilogue
     const int q = warp & 3;                                 // TMEM lane quadrant
     uint8_t* ebuf = smem_epi + q * 2 * kEpiBufBytes;
@@ -781,11 +751,10 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     int buf = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    uint32_t* pending_sig = nullptr;                        // RS: counter of the previous pushed tile
     const uint32_t parity = p.epoch & 1u;
-    Tracer<kTrace> tr(p, (warp == 4 && lane == 0) ? cluster * kCtaGroup + static_cast<int>(cta_rank) : -1, 2);
-    if (!(warp == 4 && lane == 0)) tr.base = nullptr;
-    for (int t = gemm_cluster; t < num_tiles; t += gemm_clusters) {
+    const size_t pitch = static_cast<size_t>(p.out_n) * kElem;
+    Tracer<kTrace> tr(p, (warp == 4 && lane == 0) ? cta : -1, 2);
+    for (int t = cluster; t < num_tiles; t += nclusters) {
       const TileCoord tc = tile_coord(p, t);
       const int row_cta = tc.m_blk * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
       const int row0 = row_cta + q * 32;
@@ -794,144 +763,53 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
       tc_fence_after();
       tr.ev(kEvAccReady, static_cast<uint32_t>(t));
 
-      const bool rs_push = p.mode == kModeRS && tc.part != p.rank;
-      const bool rs_own = p.mode == kModeRS && tc.part == p.rank;
       int out_row = row0;
-      int local_row = 0;
       int cta_tile = 0;
+      uint8_t* rs_dst = nullptr;
       if (p.mode == kModeRS) {
-        local_row = row0 - tc.part * p.part_rows;           // row inside the owner's shard
+        // row inside the owner's shard; staging slot [parity][src] at the owner (push) or
+        // [parity][owner] locally (pull)
+        out_row = row0 - tc.part * p.part_rows;
         cta_tile = ((row_cta - tc.part * p.part_rows) / kBlockM) * p.num_n_blocks + tc.n_blk;
-        out_row = rs_push ? (static_cast<int>(parity) * p.world + p.rank) * p.part_rows + local_row
-                          : local_row;
+        const size_t slot_bytes = static_cast<size_t>(p.part_rows) * pitch;
+        rs_dst = p.rs_transport == kRsPush
+                     ? p.stage_base[tc.part] + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes
+                     : p.stage_base[p.rank] + (static_cast<size_t>(parity) * p.world + tc.part) * slot_bytes;
       } else if (p.mode == kModeAGAfter) {
         out_row = p.rank * p.part_rows + row0;
       }
-      if (pending_sig != nullptr) {
-        // previous tile's remote stores: complete them, then publish its counter
-        if (lane == 0) {
-          bulk_wait<0>();
-          fence_proxy_async();
-          red_add_release_sys(pending_sig, 1u);
-        }
-        pending_sig = nullptr;
-      }
-      if (rs_own) {
-        if (lane < p.world && lane != p.rank)
-          wait_flag_ge<true>(p.sig_local + p.rs_sig_off + lane * p.rs_tiles_per_src + cta_tile,
-                             4u * p.epoch);
-        __syncwarp();
-        tr.ev(kEvOwnWaited, static_cast<uint32_t>(t));
-      }
 
-      if constexpr (kF32) {
-        // fp32 output: 32 columns (one 128-byte row segment) per step, no packing
 #pragma unroll 1
-        for (int c = 0; c < kBlockN / 32; ++c) {
-          uint32_t v[32];
+      for (int c = 0; c < kBlockN / kRowElems; ++c) {
+        // 32 rows x 128 bytes of output per step: this lane's row, as 32 words
+        uint32_t packed[32];
+        if constexpr (kF32) {
           const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                                  static_cast<uint32_t>(acc * kBlockN + c * 32);
-          tmem_ld_32x32b_x32(taddr, &v[0]);
+          tmem_ld_32x32b_x32(taddr, &packed[0]);
           tmem_ld_wait();
-
-          if (rs_own) {
-            const int lr = local_row + lane;
-            for (int s = 0; s < p.world; ++s) {
-              if (s == p.rank) continue;
-              const size_t row = static_cast<size_t>(parity * p.world + s) * p.part_rows + lr;
-              const uint4* src = reinterpret_cast<const uint4*>(
-                  p.stage_local + (row * p.out_n + n0 + c * 32) * 4);
+          if (p.act != kActNone) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j) {
-                const uint4 raw = __ldcg(src + j);
-                v[4 * j] = __float_as_uint(__uint_as_float(v[4 * j]) + __uint_as_float(raw.x));
-                v[4 * j + 1] = __float_as_uint(__uint_as_float(v[4 * j + 1]) + __uint_as_float(raw.y));
-                v[4 * j + 2] = __float_as_uint(__uint_as_float(v[4 * j + 2]) + __uint_as_float(raw.z));
-                v[4 * j + 3] = __float_as_uint(__uint_as_float(v[4 * j + 3]) + __uint_as_float(raw.w));
-              }
-            }
+            for (int i = 0; i < 32; ++i)
+              packed[i] = __float_as_uint(apply_act(__uint_as_float(packed[i]), p.act));
           }
-
-          if (lane == 0) bulk_wait_read<1>();
-          __syncwarp();
-          const uint32_t sbase = smem_u32(ebuf + buf * kEpiBufBytes);
-          const uint32_t srow = sbase + lane * 128;
+        } else {
+          uint32_t v[64];
+          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                                 static_cast<uint32_t>(acc * kBlockN + c * 64);
+          tmem_ld_32x32b_x32(taddr, &v[0]);
+          tmem_ld_32x32b_x32(taddr + 32, &v[32]);
+          tmem_ld_wait();
+          if (p.act != kActNone) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t dst = srow + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(v[4 * j]),
-                         "r"(v[4 * j + 1]), "r"(v[4 * j + 2]), "r"(v[4 * j + 3])
-                         : "memory");
+            for (int i = 0; i < 64; ++i) v[i] = __float_as_uint(apply_act(__uint_as_float(v[i]), p.act));
           }
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            if (p.mode == kModeAGAfter) {
-              for (int d = 0; d < p.world; ++d) tma_store_2d(&p.tmOut[d], sbase, n0 + c * 32, out_row);
-            } else {
-              tma_store_2d(&p.tmOut[p.mode == kModeRS ? tc.part : p.rank], sbase, n0 + c * 32, out_row);
-            }
-            bulk_commit();
-          }
-          buf ^= 1;
-        }
-      } else {
-#pragma unroll 1
-      for (int c = 0; c < kBlockN / 64; ++c) {
-        uint32_t v[64];
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
-                               static_cast<uint32_t>(acc * kBlockN + c * 64);
-        tmem_ld_32x32b_x32(taddr, &v[0]);
-        tmem_ld_32x32b_x32(taddr + 32, &v[32]);
-        tmem_ld_wait();
-
-        if (rs_own) {
-          const int lr = local_row + lane;
-          if constexpr ((kVariant & 2) != 0) {
-            // two sources in flight: 16 independent 16-byte loads before the first add
-            const size_t col = static_cast<size_t>(n0 + c * 64);
-            for (int i = 1; i < p.world; i += 2) {
-              int s0 = p.rank + i, s1 = p.rank + i + 1;
-              s0 = s0 >= p.world ? s0 - p.world : s0;
-              s1 = s1 >= p.world ? s1 - p.world : s1;
-              const bool two = i + 1 < p.world;
-              const size_t row0 = static_cast<size_t>(parity * p.world + s0) * p.part_rows + lr;
-              const size_t row1 = static_cast<size_t>(parity * p.world + (two ? s1 : s0)) * p.part_rows + lr;
-              const uint4* src0 = reinterpret_cast<const uint4*>(p.stage_local + (row0 * p.out_n + col) * 2);
-              const uint4* src1 = reinterpret_cast<const uint4*>(p.stage_local + (row1 * p.out_n + col) * 2);
-              uint4 r0[8], r1[8];
 #pragma unroll
-              for (int j = 0; j < 8; ++j) r0[j] = __ldcg(src0 + j);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) r1[j] = __ldcg(src1 + j);
-#pragma unroll
-              for (int j = 0; j < 8; ++j) add_packed8(&v[8 * j], r0[j], bf16);
-              if (two) {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) add_packed8(&v[8 * j], r1[j], bf16);
-              }
-            }
-          } else {
-          for (int s = 0; s < p.world; ++s) {
-            if (s == p.rank) continue;
-            const size_t row = static_cast<size_t>(parity * p.world + s) * p.part_rows + lr;
-            const uint4* src = reinterpret_cast<const uint4*>(
-                p.stage_local + (row * p.out_n + n0 + c * 64) * 2);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const uint4 raw = __ldcg(src + j);
-              add_packed8(&v[8 * j], raw, bf16);
-            }
-          }
-          }
+          for (int i = 0; i < 32; ++i)
+            packed[i] = pack2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]), bf16);
         }
 
-        uint32_t packed[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-          packed[i] = pack2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]), bf16);
-
-        if (lane == 0) bulk_wait_read<1>();     // the store that last used this buffer has read it
+        if (lane == 0) bulk_wait_read<1>();     // the TMA store that last used this buffer has read it
         __syncwarp();
         const uint32_t sbase = smem_u32(ebuf + buf * kEpiBufBytes);
         const uint32_t srow = sbase + lane * 128;
@@ -942,43 +820,40 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
                        "r"(packed[4 * j + 1]), "r"(packed[4 * j + 2]), "r"(packed[4 * j + 3])
                        : "memory");
         }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if constexpr ((kVariant & 4) != 0) {
-          // push variant: peers are written with 128-bit stores from the staged rows, only
-          // local destinations go through TMA
-          const size_t pitch = static_cast<size_t>(p.out_n) * 2;
-          const int colb = (n0 + c * 64) * 2;
-          if (rs_push) {
-            store_chunk_st128(p.out_raw[tc.part], pitch, out_row, colb, 2 * p.world * p.part_rows,
-                              p.out_n * 2, sbase, lane);
-          } else if (p.mode == kModeAGAfter) {
-            for (int d = 0; d < p.world; ++d)
-              if (d != p.rank)
-                store_chunk_st128(p.out_raw[d], pitch, out_row, colb, p.world * p.part_rows,
-                                  p.out_n * 2, sbase, lane);
-            if (lane == 0) {
-              tma_store_2d(&p.tmOut[p.rank], sbase, n0 + c * 64, out_row);
-              bulk_commit();
-            }
-          } else if (lane == 0) {
-            tma_store_2d(&p.tmOut[p.mode == kModeRS ? tc.part : p.rank], sbase, n0 + c * 64, out_row);
+        const int col0 = n0 + c * kRowElems;
+        const int colb = col0 * kElem;
+        if (p.mode == kModeRS) {
+          __syncwarp();
+          store_chunk_st128<false>(rs_dst, pitch, out_row, colb, static_cast<int>(pitch), sbase, lane);
+          __syncwarp();            // every lane has read the staged rows before they are reused
+        } else if (p.mode == kModeAGAfter && p.epi_transport == kEpiMulticast) {
+          __syncwarp();
+          store_chunk_st128<true>(p.mc_ptr, pitch, out_row, colb, static_cast<int>(pitch), sbase, lane);
+          __syncwarp();
+        } else if (p.mode == kModeAGAfter && p.epi_transport == kEpiSt128) {
+          fence_proxy_async_smem();
+          __syncwarp();
+          for (int d = 0; d < p.world; ++d)
+            if (d != p.rank)
+              store_chunk_st128<false>(p.out_raw[d], pitch, out_row, colb, static_cast<int>(pitch), sbase, lane);
+          if (lane == 0) {
+            tma_store_2d(&p.tmOut[p.rank], sbase, col0, out_row);
             bulk_commit();
           }
-          __syncwarp();            // every lane has read the staged rows before they are reused
+          __syncwarp();
         } else {
-        if (lane == 0) {
-          if (p.mode == kModeAGAfter) {
-            for (int d = 0; d < p.world; ++d) tma_store_2d(&p.tmOut[d], sbase, n0 + c * 64, out_row);
-          } else {
-            // RS: the owner's staging (or own shard) map; otherwise this rank's C
-            tma_store_2d(&p.tmOut[p.mode == kModeRS ? tc.part : p.rank], sbase, n0 + c * 64, out_row);
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (p.mode == kModeAGAfter) {
+              for (int d = 0; d < p.world; ++d) tma_store_2d(&p.tmOut[d], sbase, col0, out_row);
+            } else {
+              tma_store_2d(&p.tmOut[p.rank], sbase, col0, out_row);
+            }
+            bulk_commit();
           }
-          bulk_commit();
-        }
         }
         buf ^= 1;
-      }
       }
       tc_fence_before();
       __syncwarp();
@@ -987,46 +862,30 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         else mbar_arrive(bar_tempty + acc * 8);
       }
       tr.ev(kEvTileStored, static_cast<uint32_t>(t));
-      if constexpr ((kVariant & 4) != 0) {
-        if (rs_push) {
-          __threadfence_system();          // this lane's peer stores are performed
-          __syncwarp();
-          if (lane == 0)
-            red_add_release_sys(p.sig_peer[tc.part] + p.rs_sig_off + p.rank * p.rs_tiles_per_src + cta_tile, 1u);
-        }
-      } else if constexpr ((kVariant & 1) != 0) {
-        if (rs_push && lane == 0) {
-          // announce now: the accumulator is already released, only this warp waits
-          bulk_wait<0>();
-          fence_proxy_async();
-          red_add_release_sys(p.sig_peer[tc.part] + p.rs_sig_off + p.rank * p.rs_tiles_per_src + cta_tile, 1u);
-        }
-      } else {
-      if (rs_push)
-        pending_sig = p.sig_peer[tc.part] + p.rs_sig_off + p.rank * p.rs_tiles_per_src + cta_tile;
+      if (p.mode == kModeRS) {
+        // announce the tile to its owner as soon as this warp's stores have been performed
+        // (the accumulator is already released, only this warp waits for the round trip)
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) red_add_release_sys(p.sig_peer[tc.part] + kSigChunk + cta_tile, 1u);
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
-    if (lane == 0) {
-      bulk_wait<0>();
-      if (pending_sig != nullptr) {
-        fence_proxy_async();
-        red_add_release_sys(pending_sig, 1u);
-      }
-    }
+    if (lane == 0) bulk_wait<0>();
     tr.ev(kEvEnd, 0);
     if (p.mode == kModeAGAfter && p.world > 1) {
       // every CTA tells every peer that its share of C has landed, then waits for
       // all CTAs of all peers so that C is complete when this kernel ends
-      if constexpr ((kVariant & 4) != 0) __threadfence_system();
+      if (p.epi_transport != kEpiTma) __threadfence_system();
       if (lane == 0) { fence_proxy_async(); fence_acq_rel_sys(); }
       named_bar_sync(1, 128);
       if (warp == 4 && lane < p.world && lane != p.rank) {
         red_add_release_sys(p.sig_peer[lane] + kSigDone + p.rank, 1u);
-        wait_flag_ge<true>(p.sig_local + kSigDone + lane,
-                           p.epoch * static_cast<uint32_t>(nclusters * kCtaGroup));
+        wait_flag_ge<true>(p.sig_local + kSigDone + lane, p.epoch * static_cast<uint32_t>(nctas));
       }
     }
+    // RS: help the aux warps with whatever is left of the reduction
+    if (p.mode == kModeRS) rs_reduce_loop(p, lane, bf16);
   }
 
   // ---------------------------------------------------------------- teardown
@@ -1037,25 +896,25 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
 }
 
 // One rank per process / GPU: parameters in the kernel parameter space.
-template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kTrace = false,
-          int kVariant = 0>
-__global__ void __launch_bounds__(kNumThreads, 1)
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kSplit = false,
+          bool kTrace = false>
+__global__ void __launch_bounds__(kMaxThreads, 1)
 tp_gemm_kernel(const __grid_constant__ TpGemmParams p) {
   const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
   const int nclusters = kCtaGroup == 2 ? static_cast<int>(num_clusters_x()) : static_cast<int>(gridDim.x);
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kTrace, kVariant>(p, cluster, nclusters);
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kSplit, kTrace>(p, cluster, nclusters);
 }
 
 // Several ranks emulated by ONE launch on one GPU (tests): the grid is split into
 // `world` equal groups of clusters, group r runs rank r's parameter block. All
 // CTAs of one launch are co-resident (grid <= SM count), so ranks that wait on
 // each other make progress, which separate launches on one GPU cannot guarantee.
-template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, int kVariant = 0>
-__global__ void __launch_bounds__(kNumThreads, 1)
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kSplit = false>
+__global__ void __launch_bounds__(kMaxThreads, 1)
 tp_gemm_emulated_kernel(const TpGemmParams* __restrict__ plist, int clusters_per_rank) {
   const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
   const int vr = cluster / clusters_per_rank;
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, false, kVariant>(
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kSplit, false>(
       plist[vr], cluster - vr * clusters_per_rank, clusters_per_rank);
 }
 

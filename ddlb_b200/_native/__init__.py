@@ -18,7 +18,11 @@ IPC_HANDLE_BYTES = 64
 MODE_PLAIN, MODE_AG_BEFORE, MODE_AG_AFTER, MODE_RS = 0, 1, 2, 3
 DTYPE_F16, DTYPE_BF16, DTYPE_F32 = 0, 1, 2
 B_KN, B_NK = 0, 1
-COMM_EVERY_CTA, COMM_PULL_CTAS, COMM_PUSH_CTAS, COMM_EVERY_CTA_TMA, COMM_EVERY_CTA_PULL = 0, 1, 2, 3, 4
+AG_PULL, AG_PUSH, AG_PUSH_MULTICAST = 0, 1, 2
+EPI_TMA, EPI_ST128, EPI_MULTICAST = 0, 1, 2
+RS_PUSH, RS_PULL, RS_PULL_MULTICAST = 0, 1, 2
+FP32_3XTF32, FP32_TF32 = 0, 1
+ACT_NONE, ACT_RELU, ACT_SILU, ACT_GELU_TANH = 0, 1, 2, 3
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libddlb_b200.so")
@@ -30,17 +34,19 @@ class NativeError(RuntimeError):
 
 
 class TpGemmConfig(Structure):
+    """Mirror of ``ddlb_tp_gemm_config`` (``include/ddlb_b200.h``)."""
     _fields_ = [
         ("mode", c_int32), ("dtype", c_int32), ("b_layout", c_int32), ("cta_group", c_int32),
-        ("block_n", c_int32), ("group_m", c_int32), ("num_sms", c_int32), ("n_comm_ctas", c_int32),
-        ("rank", c_int32), ("world", c_int32), ("chunk_rows", c_int32), ("comm_transport", c_int32),
+        ("block_n", c_int32), ("group_m", c_int32), ("num_sms", c_int32),
+        ("rank", c_int32), ("world", c_int32), ("chunk_rows", c_int32),
+        ("ag_transport", c_int32), ("epi_transport", c_int32), ("rs_transport", c_int32),
+        ("unrotated", c_int32), ("fp32_mode", c_int32), ("epilogue_act", c_int32),
         ("m", c_int64), ("n", c_int64), ("k", c_int64),
         ("a", c_void_p), ("b", c_void_p),
         ("out", c_void_p * MAX_WORLD), ("peer_a", c_void_p * MAX_WORLD),
-        ("stage_local", c_void_p),
+        ("stage", c_void_p * MAX_WORLD), ("mc_ptr", c_void_p),
         ("sig_local", c_void_p), ("sig_peer", c_void_p * MAX_WORLD),
         ("trace", c_void_p),
-        ("variant", c_int32), ("reserved", c_int32),
     ]
 
 

@@ -61,14 +61,28 @@ def describe_implementation(impl_class, base_impl: str, options: Dict[str, Any])
     """``(label, option_string)`` for a result row.
 
     The label excludes ``size`` exactly like the reference
-    (``benchmark.py:106-119``); the option string keeps it.
+    (``benchmark.py:106-119``); the option string keeps it. Classes that serve a
+    reference implementation NAME with the native kernel (``SERVED_BY``, see
+    ``primitives/TPColumnwise/compat.py``) are labelled ``fused[as <name>]`` and list the
+    options that have no equivalent under ``ignored:`` so a results file never attributes
+    native-kernel timings to nvFuser / Transformer Engine / JAX.
     """
     keys = [k for k in getattr(impl_class, "DEFAULT_OPTIONS", {}) if k in options]
+    ignored = []
+    honoured = getattr(impl_class, "honoured_options", None)
+    if honoured is not None:
+        keep = honoured(options)
+        ignored = [k for k in keys if k not in keep]
+        keys = [k for k in keys if k in keep]
     shown = [k for k in keys if k != "size"]
-    label = base_impl
+    served_by = getattr(impl_class, "SERVED_BY", None)
+    label = f"{served_by}[as {base_impl}]" if served_by else base_impl
     if shown:
         label += " (" + ", ".join(f"{k}={options[k]}" for k in shown) + ")"
     option_str = ", ".join(f"{k}={options[k]}" for k in keys)
+    if ignored:
+        option_str += ("; " if option_str else "") + "ignored: " + ",".join(
+            f"{k}={options[k]}" for k in ignored)
     return label, option_str
 
 
@@ -178,7 +192,6 @@ def time_implementation(impl, num_iterations: int, backend: str, barrier: bool):
             starts = [torch.cuda.Event(enable_timing=True) for _ in range(num_iterations)]
             ends = [torch.cuda.Event(enable_timing=True) for _ in range(num_iterations)]
             if comm.world_size > 1:
-                comm.init_process_group()
                 comm.symmetric_heap()          # every implementation gets the device barrier
             comm.barrier()
             flush = _L2Flusher(comm)

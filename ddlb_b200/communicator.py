@@ -7,8 +7,12 @@ whole life cycle:
 
 * rank / device selection (CUDA when present, otherwise a CPU mode so the
   harness, the ``gloo`` baseline and the tests run without a GPU);
-* ONE ``torch.distributed`` process group per benchmark child, used only for
-  plumbing (handle exchange, max-over-ranks of timings, baselines);
+* an own bootstrap: a key-value store (file store of the in-tree launcher, torchrun's agent
+  store, or a TCP store hosted by rank 0) carries the handle exchange, host barriers and the
+  max-over-ranks of timings, so the fused product path never creates an NCCL communicator
+  (the reference boots every implementation through NCCL, ``TPColumnwise/pytorch.py:53-59``);
+* a ``torch.distributed`` process group only when a library baseline asks for one
+  (``pytorch;backend=nccl|gloo``);
 * the native symmetric heap (peer-mapped buffers + signal pads, see
   ``ddlb_b200/parallel/symm_heap.py``) and the device-side barrier that the
   fused kernels and the timing loop use;
@@ -62,6 +66,8 @@ class Communicator:
 
         self._pg_owned = False
         self._symm = None
+        self._store = None
+        self._store_round = 0
         self._sequence = int(os.environ.get("DDLB_CHILD_SEQUENCE", "0"))
         self._initialized = True
 
@@ -79,13 +85,78 @@ class Communicator:
                 f"local_rank={self.local_rank}, local_size={self.local_size}, "
                 f"device={self.device})")
 
+    # ---------------------------------------------------------------- bootstrap
+    def store(self):
+        """The run's key-value store (created on first use, one per benchmark child).
+
+        Collision-proof choices first (a guessed TCP port can be taken, and a rank that
+        fails to bind leaves its peers hanging in the rendezvous):
+        * one rank: an in-process ``HashStore``;
+        * in-tree launcher (``DDLB_RDZV_PREFIX``): a ``FileStore`` in a fresh directory,
+          one file per child sequence number;
+        * torchrun (agent store on ``MASTER_PORT``): a ``PrefixStore`` over a client of
+          that store, keyed by the child sequence number;
+        * otherwise (mpirun / SLURM style): a ``TCPStore`` hosted by rank 0 on
+          ``DDLB_MASTER_ADDR:port`` with the port rotating per child (the reference reuses
+          one port, ``ddlb/envs.py:75-77``).
+        """
+        if self._store is not None:
+            return self._store
+        import datetime
+        import torch.distributed as dist
+        seq = self._sequence
+        timeout = datetime.timedelta(seconds=int(os.environ.get("DDLB_STORE_TIMEOUT", "300")))
+        prefix = os.environ.get("DDLB_RDZV_PREFIX")
+        if self.world_size == 1:
+            store = dist.HashStore()
+        elif prefix:
+            store = dist.FileStore(f"{prefix}_{seq}", self.world_size)
+        elif (os.environ.get("TORCHELASTIC_USE_AGENT_STORE", "").lower() == "true"
+                and os.environ.get("MASTER_PORT") and os.environ.get("MASTER_ADDR")):
+            base = dist.TCPStore(os.environ["MASTER_ADDR"], int(os.environ["MASTER_PORT"]),
+                                 self.world_size, is_master=False, timeout=timeout)
+            run = os.environ.get("TORCHELASTIC_RUN_ID", "run")
+            store = dist.PrefixStore(f"ddlb_b200/{run}/{seq}", base)
+        else:
+            store = dist.TCPStore(envs.get_master_addr(), envs.rendezvous_port(seq),
+                                  self.world_size, is_master=(self.rank == 0), timeout=timeout,
+                                  wait_for_workers=False)
+        try:
+            store.set_timeout(timeout)
+        except Exception:
+            pass
+        self._store = store
+        return store
+
+    def all_gather_bytes(self, payload: bytes) -> List[bytes]:
+        """One byte string from every rank, through the store (handle exchange)."""
+        if self.world_size == 1:
+            return [payload]
+        store = self.store()
+        self._store_round += 1
+        tag = f"ag/{self._store_round}"
+        store.set(f"{tag}/{self.rank}", payload)
+        return [bytes(store.get(f"{tag}/{r}")) for r in range(self.world_size)]
+
+    def host_barrier(self) -> None:
+        """Meet the other rank PROCESSES (no device work involved)."""
+        if self.world_size > 1:
+            self.all_gather_bytes(b"1")
+
+    def all_reduce_max(self, values: List[float]) -> List[float]:
+        """Element-wise max over ranks (reference ``ddlb/benchmark.py:191-204``), through
+        the store: it is off the measured path and needs no communicator."""
+        if self.world_size == 1:
+            return list(values)
+        import struct
+        mine = struct.pack(f"<{len(values)}d", *values)
+        rows = [struct.unpack(f"<{len(values)}d", b) for b in self.all_gather_bytes(mine)]
+        return [max(col) for col in zip(*rows)] if values else []
+
     # ----------------------------------------------------------- process group
     def init_process_group(self, backend: Optional[str] = None) -> None:
-        """Create the process group if none exists yet (idempotent).
-
-        The rendezvous store is chosen by ``_rendezvous``. When the default group
-        already exists it is reused.
-        """
+        """Create a ``torch.distributed`` process group for a LIBRARY baseline (idempotent).
+        The fused implementations never call this."""
         import torch.distributed as dist
 
         if dist.is_initialized():
@@ -102,44 +173,9 @@ class Communicator:
         kwargs: Dict[str, Any] = {}
         if backend == "nccl":
             kwargs["device_id"] = self.device
-        store, init_method = self._rendezvous()
-        if store is not None:
-            dist.init_process_group(backend=backend, rank=self.rank, world_size=self.world_size,
-                                    store=store, **kwargs)
-        else:
-            dist.init_process_group(backend=backend, rank=self.rank, world_size=self.world_size,
-                                    init_method=init_method, **kwargs)
+        dist.init_process_group(backend=backend, rank=self.rank, world_size=self.world_size,
+                                store=dist.PrefixStore("pg", self.store()), **kwargs)
         self._pg_owned = True
-
-    def _rendezvous(self):
-        """``(store, init_method)`` for this child; exactly one is not None.
-
-        Collision-proof choices first (a guessed TCP port can be taken, and a rank that
-        fails to bind leaves its peers hanging in the rendezvous):
-        * one rank: an in-process ``HashStore``;
-        * in-tree launcher (``DDLB_RDZV_PREFIX``): a ``FileStore`` in a fresh directory,
-          one file per child sequence number;
-        * torchrun (agent store on ``MASTER_PORT``): a ``PrefixStore`` over a client of
-          that store, keyed by the child sequence number;
-        * otherwise (mpirun / SLURM style): ``tcp://DDLB_MASTER_ADDR:port`` with the port
-          rotating per child (the reference reuses one port, ``ddlb/envs.py:75-77``).
-        """
-        import datetime
-        import torch.distributed as dist
-        seq = self._sequence
-        if self.world_size == 1:
-            return dist.HashStore(), None
-        prefix = os.environ.get("DDLB_RDZV_PREFIX")
-        if prefix:
-            return dist.FileStore(f"{prefix}_{seq}", self.world_size), None
-        if (os.environ.get("TORCHELASTIC_USE_AGENT_STORE", "").lower() == "true"
-                and os.environ.get("MASTER_PORT") and os.environ.get("MASTER_ADDR")):
-            base = dist.TCPStore(os.environ["MASTER_ADDR"], int(os.environ["MASTER_PORT"]),
-                                 self.world_size, is_master=False,
-                                 timeout=datetime.timedelta(seconds=300))
-            run = os.environ.get("TORCHELASTIC_RUN_ID", "run")
-            return dist.PrefixStore(f"ddlb_b200/{run}/{seq}", base), None
-        return None, f"tcp://{envs.get_master_addr()}:{envs.rendezvous_port(seq)}"
 
     @property
     def pg_initialized(self) -> bool:
@@ -149,57 +185,47 @@ class Communicator:
     def barrier(self) -> None:
         """Host-visible barrier: drain this device, then meet the other ranks."""
         import torch
-        import torch.distributed as dist
 
         if self.is_cuda:
             torch.cuda.synchronize()
-        if self.world_size > 1 and dist.is_available() and dist.is_initialized():
+        if self.world_size > 1:
             if self._symm is not None:
                 # device barrier on the signal pads + host wait: no NCCL launch
                 self._symm.barrier()
                 torch.cuda.synchronize()
             else:
-                dist.barrier()
-
-    def all_reduce_max(self, values: List[float]) -> List[float]:
-        """Element-wise max over ranks (reference ``ddlb/benchmark.py:191-204``)."""
-        import torch
-        import torch.distributed as dist
-
-        if self.world_size == 1:
-            return list(values)
-        self.init_process_group()
-        t = torch.tensor(values, dtype=torch.float64, device=self.device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return t.tolist()
-
-    def all_gather_bytes(self, payload: bytes) -> List[bytes]:
-        """Gather one fixed-size byte string from every rank (handle exchange)."""
-        import torch
-        import torch.distributed as dist
-
-        if self.world_size == 1:
-            return [payload]
-        self.init_process_group()
-        mine = torch.frombuffer(bytearray(payload), dtype=torch.uint8).to(self.device)
-        out = torch.empty(self.world_size * mine.numel(), dtype=torch.uint8, device=self.device)
-        dist.all_gather_into_tensor(out, mine)
-        raw = out.cpu().numpy().tobytes()
-        n = len(payload)
-        return [raw[i * n:(i + 1) * n] for i in range(self.world_size)]
+                self.host_barrier()
 
     # ---------------------------------------------------------- symmetric heap
     def symmetric_heap(self, min_bytes: int = 0):
-        """The rank's symmetric heap (created on first use, grown never)."""
+        """The rank's symmetric heap (created on first use, grown never).
+
+        ``DDLB_SYMM_MODE``: ``ipc`` - one ``cudaMalloc`` arena exported with cudaIpc;
+        ``vmm`` - cuMem allocations exchanged as POSIX file descriptors, with an NVLS
+        multicast window when the devices support it (required by the ``multimem``
+        transports); ``auto`` (default) - ``vmm`` when every rank can set it up, else ``ipc``.
+        """
         if not self.is_cuda:
             raise RuntimeError("the symmetric heap needs CUDA devices")
         if self._symm is None:
-            if os.environ.get("DDLB_SYMM_MODE", "ipc") == "vmm":     # experimental, see vmm_heap.py
-                from .parallel.vmm_heap import VmmHeap
-                self._symm = VmmHeap(self, min_bytes)
-            else:
+            mode = os.environ.get("DDLB_SYMM_MODE", "auto").lower()
+            if mode not in ("auto", "ipc", "vmm"):
+                raise ValueError(f"DDLB_SYMM_MODE must be auto, ipc or vmm (got {mode!r})")
+            heap = None
+            if mode in ("auto", "vmm") and self.world_size > 1:
+                from .parallel.vmm_heap import VmmHeap, VmmUnavailable
+                try:
+                    heap = VmmHeap(self, min_bytes)
+                except VmmUnavailable as exc:
+                    if mode == "vmm":
+                        raise
+                    if self.rank == 0:
+                        print(f"[ddlb_b200] VMM/NVLS heap unavailable ({exc}); using cudaIpc",
+                              flush=True)
+            if heap is None:
                 from .parallel.symm_heap import SymmetricHeap
-                self._symm = SymmetricHeap(self, min_bytes)
+                heap = SymmetricHeap(self, min_bytes)
+            self._symm = heap
         elif min_bytes > self._symm.capacity:
             raise RuntimeError(
                 f"symmetric heap already created with {self._symm.capacity} B; "
@@ -225,6 +251,7 @@ class Communicator:
             except Exception:
                 pass
             self._pg_owned = False
+        self._store = None
 
     @classmethod
     def reset(cls) -> None:

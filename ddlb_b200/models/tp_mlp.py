@@ -8,13 +8,15 @@ sequence-sharded ``[m/d, h]``;
     down:  Y = reduce_scatter_rows( H @ W_down[f/d, h] )    -> tp_rowwise   (GEMM -> RS)
 
 and leave sequence-sharded ``[m/d, h]``. Both GEMMs run on the fused sm_100a kernels; the
-activation is applied in between (a fused epilogue activation is future work). The
+activation (``relu`` / ``silu`` / ``gelu_tanh``) is applied to the fp32 accumulator inside the
+up kernel's epilogue, whose output buffer IS the down kernel's A operand: a forward pass is
+exactly two kernel launches, no elementwise kernel and no copy. The
 reference has no model code; its closest relatives are the two benchmark primitives
 themselves (``ddlb/primitives/TPColumnwise``, ``ddlb/primitives/TPRowwise``).
 """
 from __future__ import annotations
 
-from typing import Callable, Optional
+from typing import Optional
 
 LLAMA3_70B_MLP = {"hidden": 8192, "ffn": 28672}
 
@@ -28,7 +30,7 @@ class TPMLP:
     """
 
     def __init__(self, heap, rank: int, world: int, tokens: int, hidden: int, ffn: int, dtype,
-                 w_up, w_down, activation: Optional[Callable] = None, **kernel_opts):
+                 w_up, w_down, activation: Optional[str] = "silu", **kernel_opts):
         import torch
         from ..ops.tp_gemm import FusedAllGatherGemm, FusedGemmReduceScatter
         if ffn % world or tokens % world:
@@ -40,22 +42,27 @@ class TPMLP:
                 f"{tuple(w_up.shape)} and {tuple(w_down.shape)}")
         self.rank, self.world = rank, world
         self.tokens, self.hidden, self.ffn = tokens, hidden, ffn
-        self.activation = activation if activation is not None else torch.nn.functional.silu
+        self.activation = activation
+        # H[tokens, f_local]: written by the up kernel's epilogue, read by the down kernel's TMA
+        self._h = torch.empty(tokens, f_local, dtype=dtype, device=w_up.device)
         # up projection: global problem [tokens, hidden] x [hidden, f_local]
         self.up = FusedAllGatherGemm(heap, rank, world, tokens, f_local, hidden, dtype, w_up,
-                                     order="AG_before", **kernel_opts)
+                                     order="AG_before", activation=activation, out=self._h,
+                                     **kernel_opts)
         # down projection: every rank holds H[tokens, f_local]; k of the global problem = ffn
-        self._h = torch.empty(tokens, f_local, dtype=dtype, device=w_up.device)
         self.down = FusedGemmReduceScatter(heap, rank, world, tokens, hidden, ffn, dtype,
                                            self._h, w_down, **kernel_opts)
         self.x_shard = self.up.a_shard             # write the rank's activations here
 
     def forward(self, x_shard=None):
-        """Returns this rank's ``[tokens/world, hidden]`` rows of the block output."""
+        """Returns this rank's ``[tokens/world, hidden]`` rows of the block output.
+
+        ``x_shard`` may be overwritten as soon as the previous ``forward`` has completed on
+        this rank's stream: the up kernel ends only after every peer has finished reading it.
+        """
         if x_shard is not None:
             self.x_shard.copy_(x_shard)
-        h = self.up.run()                          # [tokens, f_local], one kernel
-        self._h.copy_(self.activation(h))
+        self.up.run()                              # H = act(allgather(X) @ W_up), one kernel
         return self.down.run()                     # [tokens/world, hidden], one kernel
 
     __call__ = forward

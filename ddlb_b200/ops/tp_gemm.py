@@ -4,13 +4,27 @@
 resolved once, ``run()`` is a single kernel launch on the current stream.
 ``FusedAllGatherGemm`` / ``FusedGemmReduceScatter`` add the symmetric buffers and
 signal words a multi-rank op needs; ``gemm()`` is the single-GPU convenience call.
+
+float32 runs on the tensor cores as 3xTF32 (``fp32_mode="3xtf32"``, default: both operands
+are split into tf32 hi + lo parts in shared memory and three ``kind::tf32`` MMAs are issued
+per k-step) or as one TF32 pass (``"tf32"``). Either way B must be ``[n,k]``; the wrappers
+transpose a ``[k,n]`` weight ONCE at construction (the reference's Transformer-Engine
+implementation does the same with its weight, ``TPColumnwise/transformer_engine.py:69-71``).
 """
 from __future__ import annotations
 
 import ctypes
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, Optional, Sequence
 
 from .. import _native as N
+
+AG_TRANSPORTS = {"pull": N.AG_PULL, "push": N.AG_PUSH, "multimem": N.AG_PUSH_MULTICAST}
+EPI_TRANSPORTS = {"tma": N.EPI_TMA, "st128": N.EPI_ST128, "multimem": N.EPI_MULTICAST}
+RS_TRANSPORTS = {"push": N.RS_PUSH, "pull": N.RS_PULL, "multimem": N.RS_PULL_MULTICAST}
+FP32_MODES = {"3xtf32": N.FP32_3XTF32, "tf32": N.FP32_TF32}
+ACTIVATIONS = {None: N.ACT_NONE, "none": N.ACT_NONE, "relu": N.ACT_RELU, "silu": N.ACT_SILU,
+               "gelu_tanh": N.ACT_GELU_TANH}
+
 
 def _dtype_code(t) -> int:
     import torch
@@ -19,18 +33,16 @@ def _dtype_code(t) -> int:
     if t == torch.bfloat16:
         return N.DTYPE_BF16
     if t == torch.float32:
-        if not tf32_enabled():
-            raise TypeError(
-                "float32 runs through the kind::tf32 kernels, which have not been validated on "
-                "hardware yet; set DDLB_ENABLE_TF32=1 to use them, or use the pytorch baseline")
         return N.DTYPE_F32
-    raise TypeError(f"the tcgen05 kernels take float16/bfloat16 (and float32 via TF32), got {t}")
+    raise TypeError(f"the tcgen05 kernels take float16/bfloat16/float32, got {t}")
 
 
-def tf32_enabled() -> bool:
-    """float32 inputs via kind::tf32 MMAs: opt-in until validated on a B200."""
-    import os
-    return os.environ.get("DDLB_ENABLE_TF32", "0") == "1"
+def _weight_for_kernel(b, b_is_nk: bool):
+    """fp32 operands must be K-major for the tensor cores: ``[k,n]`` weights are transposed once."""
+    import torch
+    if b.dtype == torch.float32 and not b_is_nk:
+        return b.t().contiguous(), True
+    return b, b_is_nk
 
 
 class TpGemmPlan:
@@ -47,7 +59,7 @@ class TpGemmPlan:
         info = (ctypes.c_int32 * 8)()
         N.check(self._lib.ddlb_tp_gemm_info(self._h, ctypes.byref(info)), "tp_gemm_info")
         self.info: Dict[str, int] = dict(zip(
-            ("grid", "cluster", "smem_bytes", "cta_group", "block_n", "stages", "n_comm_ctas",
+            ("grid", "cluster", "smem_bytes", "cta_group", "block_n", "stages", "threads",
              "chunk_rows"), list(info)))
         self.epoch = 0
         self.launches = 0
@@ -74,18 +86,26 @@ class TpGemmPlan:
 
 def _base_config(mode: int, dtype, m: int, n: int, k: int, rank: int, world: int,
                  b_layout: int, cta_group: int, block_n: int, group_m: int, num_sms: int,
-                 n_comm_ctas: int = 0, chunk_rows: int = 0, comm_transport: int = 0) -> N.TpGemmConfig:
+                 chunk_rows: int = 0, fp32_mode: str = "3xtf32",
+                 unrotated: bool = False, activation: Optional[str] = None) -> N.TpGemmConfig:
+    if fp32_mode not in FP32_MODES:
+        raise ValueError(f"fp32_mode must be one of {sorted(FP32_MODES)}, got {fp32_mode!r}")
+    if activation not in ACTIVATIONS:
+        raise ValueError(f"activation must be one of {list(ACTIVATIONS)}, got {activation!r}")
     cfg = N.TpGemmConfig()
     cfg.mode, cfg.dtype, cfg.b_layout = mode, _dtype_code(dtype), b_layout
     cfg.cta_group, cfg.block_n, cfg.group_m, cfg.num_sms = cta_group, block_n, group_m, num_sms
-    cfg.n_comm_ctas, cfg.rank, cfg.world, cfg.chunk_rows = n_comm_ctas, rank, world, chunk_rows
-    cfg.comm_transport = comm_transport
+    cfg.rank, cfg.world, cfg.chunk_rows = rank, world, chunk_rows
+    cfg.fp32_mode = FP32_MODES[fp32_mode]
+    cfg.unrotated = 1 if unrotated else 0
+    cfg.epilogue_act = ACTIVATIONS[activation]
     cfg.m, cfg.n, cfg.k = m, n, k
     return cfg
 
 
 def plain_gemm_plan(a, b, out=None, *, b_is_nk: bool = False, cta_group: int = 0,
-                    block_n: int = 0, group_m: int = 0, num_sms: int = 0):
+                    block_n: int = 0, group_m: int = 0, num_sms: int = 0,
+                    fp32_mode: str = "3xtf32", activation: Optional[str] = None):
     """Plan for ``out[m,n] = a[m,k] @ b`` with ``b`` ``[k,n]`` (or ``[n,k]`` if ``b_is_nk``)."""
     import torch
     assert a.is_cuda and b.is_cuda and a.is_contiguous() and b.is_contiguous()
@@ -95,8 +115,10 @@ def plain_gemm_plan(a, b, out=None, *, b_is_nk: bool = False, cta_group: int = 0
     assert (b.shape[1] if b_is_nk else b.shape[0]) == k
     if out is None:
         out = torch.empty(m, n, dtype=a.dtype, device=a.device)
+    b, b_is_nk = _weight_for_kernel(b, b_is_nk)
     cfg = _base_config(N.MODE_PLAIN, a.dtype, m, n, k, 0, 1, N.B_NK if b_is_nk else N.B_KN,
-                       cta_group, block_n, group_m, num_sms)
+                       cta_group, block_n, group_m, num_sms, fp32_mode=fp32_mode,
+                       activation=activation)
     cfg.a, cfg.b = a.data_ptr(), b.data_ptr()
     cfg.out[0] = out.data_ptr()
     return TpGemmPlan(cfg, keepalive=(a, b, out)), out
@@ -107,6 +129,19 @@ def gemm(a, b, out=None, **kw):
     plan, out = plain_gemm_plan(a, b, out, **kw)
     plan.run()
     return out
+
+
+def _resolve_transport(name: str, table: dict, default: str, heap, what: str) -> str:
+    """``auto`` -> the default; ``multimem`` needs a heap with an NVLS multicast window."""
+    if name in ("auto", "p2p"):
+        name = default
+    if name not in table:
+        raise ValueError(f"{what} transport must be one of {sorted(table)} (or auto), got {name!r}")
+    if name == "multimem" and not getattr(heap, "has_multicast", False):
+        raise RuntimeError(
+            f"{what} transport 'multimem' needs the VMM symmetric heap with an NVLS multicast "
+            "window (DDLB_SYMM_MODE=vmm or auto on NVSwitch systems); this heap has none")
+    return name
 
 
 class _FusedBase:
@@ -138,37 +173,43 @@ class _FusedBase:
 class FusedAllGatherGemm(_FusedBase):
     """``C[m,n] = allgather_rows(A_shard)[m,k] @ B[k,n]`` in ONE kernel per rank.
 
-    ``order="AG_before"``: the peers' shards are moved over NVLink into the local gathered
-    buffer chunk by chunk (``transport``: by two warps of every CTA through registers, by a
-    TMA warp per CTA, or by dedicated comm CTAs) while the GEMM multiplies the chunks that
-    have arrived. ``order="AG_after"``: each rank multiplies its own shard and its epilogue
-    stores the C tiles into every rank's output.
+    ``order="AG_before"``: the shards are moved over NVLink chunk by chunk by the aux warps
+    of every CTA (``transport``: ``pull`` the peers' shards - default -, ``push`` the own
+    shard to every peer, or ``multimem``: one ``multimem.st`` per 16 bytes replicated by the
+    NVSwitch) while the GEMM multiplies the chunks that have arrived. The kernel returns only
+    after every peer has finished reading this rank's shard, so the caller may overwrite
+    ``a_shard`` right after it (the guarantee ``ncclAllGather`` gives for its send buffer).
+    ``order="AG_after"``: each rank multiplies its own shard and its epilogue writes the C
+    tiles into every rank's output (``transport``: ``tma`` - default -, ``st128``,
+    ``multimem``).
     The rank's input shard must be written into ``self.a_shard`` (a view of the
     symmetric gathered buffer).
     """
 
     def __init__(self, heap, rank: int, world: int, m: int, n: int, k: int, dtype, b,
-                 order: str = "AG_before", chunk_rows: int = 0, n_comm_ctas: int = 0,
+                 order: str = "AG_before", chunk_rows: int = 0,
                  cta_group: int = 0, block_n: int = 0, group_m: int = 0, num_sms: int = 0,
-                 b_is_nk: bool = False, transport: str = "cta_pull", trace: bool = False,
-                 variant: int = 0):
+                 b_is_nk: bool = False, transport: str = "auto", trace: bool = False,
+                 fp32_mode: str = "3xtf32", unrotated: bool = False,
+                 activation: Optional[str] = None, out=None):
         super().__init__(heap, rank, world)
         import torch
         if m % world:
             raise ValueError(f"m ({m}) must be divisible by world ({world})")
-        transports = {"cta": N.COMM_EVERY_CTA, "cta_tma": N.COMM_EVERY_CTA_TMA,
-                      "cta_pull": N.COMM_EVERY_CTA_PULL,
-                      "pull": N.COMM_PULL_CTAS, "push": N.COMM_PUSH_CTAS}
-        if transport not in transports:
-            raise ValueError(f"transport must be one of {sorted(transports)}, got {transport!r}")
         rows = m // world
         self.order = order
+        b, b_is_nk = _weight_for_kernel(b, b_is_nk)
         layout = N.B_NK if b_is_nk else N.B_KN
+        common = dict(fp32_mode=fp32_mode, unrotated=unrotated, activation=activation)
+        if out is not None and order != "AG_before":
+            raise ValueError("a caller-provided output is supported for order='AG_before' only")
         if order == "AG_before":
-            self.out = [torch.empty(m, n, dtype=dtype, device=b.device)]
+            self.transport = _resolve_transport(transport, AG_TRANSPORTS, "pull", heap, "AG_before")
+            self.out = [out if out is not None else torch.empty(m, n, dtype=dtype, device=b.device)]
             cfg = _base_config(N.MODE_AG_BEFORE if world > 1 else N.MODE_PLAIN, dtype, m, n, k,
                                rank, world, layout, cta_group, block_n, group_m, num_sms,
-                               n_comm_ctas, chunk_rows, transports[transport])
+                               chunk_rows, **common)
+            cfg.ag_transport = AG_TRANSPORTS[self.transport]
             if world == 1:
                 # nothing to gather: an ordinary device buffer, no symmetric heap needed
                 self.a_gathered = torch.empty(m, k, dtype=dtype, device=b.device)
@@ -178,9 +219,12 @@ class FusedAllGatherGemm(_FusedBase):
                 cfg.a = heap.ptr(a_off)
                 for p in range(world):
                     cfg.peer_a[p] = heap.ptr(a_off, p)
+                if self.transport == "multimem":
+                    cfg.mc_ptr = heap.mc_ptr(a_off)
             self.a_shard = self.a_gathered[rank * rows:(rank + 1) * rows]
             cfg.out[rank] = self.out[0].data_ptr()
         elif order == "AG_after":
+            self.transport = _resolve_transport(transport, EPI_TRANSPORTS, "tma", heap, "AG_after")
             self.a_shard = torch.empty(rows, k, dtype=dtype, device=b.device)
             self.a_gathered = None
             if world > 1:
@@ -190,16 +234,19 @@ class FusedAllGatherGemm(_FusedBase):
                 cfgs = []
                 for off, _ in offs:
                     cfg = _base_config(N.MODE_AG_AFTER, dtype, m, n, k, rank, world, layout,
-                                       cta_group, block_n, group_m, num_sms)
+                                       cta_group, block_n, group_m, num_sms, **common)
+                    cfg.epi_transport = EPI_TRANSPORTS[self.transport]
                     cfg.a = self.a_shard.data_ptr()
                     for p in range(world):
                         cfg.out[p] = heap.ptr(off, p)
+                    if self.transport == "multimem":
+                        cfg.mc_ptr = heap.mc_ptr(off)
                     cfgs.append(cfg)
                 cfg = cfgs
             else:
                 self.out = [torch.empty(m, n, dtype=dtype, device=b.device)]
                 cfg = _base_config(N.MODE_PLAIN, dtype, m, n, k, 0, 1, layout, cta_group, block_n,
-                                   group_m, num_sms)
+                                   group_m, num_sms, **common)
                 cfg.a = self.a_shard.data_ptr()
                 cfg.out[0] = self.out[0].data_ptr()
         else:
@@ -212,7 +259,6 @@ class FusedAllGatherGemm(_FusedBase):
             self.trace_buf = alloc_trace_buffer(b.device)
         for c in cfgs:
             c.b = b.data_ptr()
-            c.variant = int(variant)          # experimental A/B schedule variants (0 = production)
             if self.trace_buf is not None:
                 c.trace = self.trace_buf.data_ptr()
         if world > 1:
@@ -249,15 +295,24 @@ class FusedAllGatherGemm(_FusedBase):
 class FusedGemmReduceScatter(_FusedBase):
     """``C_shard[m/d,n] = reduce_scatter_rows(A[m,k/d] @ B[k/d,n])`` in ONE kernel per rank.
 
-    Tiles are visited owner by owner starting with the next rank; a tile that belongs
-    to another rank is stored (TMA, P2P) into that rank's staging buffer and its
-    arrival counter bumped; the rank's own tiles come last and their epilogue adds
-    the d-1 staged partials in fp32 before the single rounding to the output type.
+    Every partial tile leaves TMEM, is rounded once to the output type and stored with 128-bit
+    stores into a staging slot; the owner's aux warps (all CTAs, work-queue) sum the d slots
+    of each 32-row x 128-byte unit in fp32 as soon as all of them have landed and write the
+    output shard. ``transport``:
+
+    * ``push`` (default): slots live at the OWNER; owners are visited ring-wise starting with
+      the next rank, the own tiles last (their partials need no NVLink); the reducers read
+      local memory.
+    * ``pull``: slots stay LOCAL; every rank visits the owners 0..d-1 in the same order and
+      the owner's reducers load the d copies over NVLink.
+    * ``multimem``: like ``pull``, but the owner issues ONE ``multimem.ld_reduce`` per
+      16 bytes and the NVSwitch adds the d copies (needs the VMM heap's multicast window).
     """
 
     def __init__(self, heap, rank: int, world: int, m: int, n: int, k: int, dtype, a, b,
                  chunk_rows: int = 0, cta_group: int = 0, block_n: int = 0, group_m: int = 0,
-                 num_sms: int = 0, b_is_nk: bool = False, trace: bool = False, variant: int = 0):
+                 num_sms: int = 0, b_is_nk: bool = False, trace: bool = False,
+                 transport: str = "auto", fp32_mode: str = "3xtf32", unrotated: bool = False):
         super().__init__(heap, rank, world)
         import torch
         self.trace_buf = None
@@ -267,24 +322,28 @@ class FusedGemmReduceScatter(_FusedBase):
         if m % world or k % world:
             raise ValueError(f"m ({m}) and k ({k}) must be divisible by world ({world})")
         rows = m // world
+        b, b_is_nk = _weight_for_kernel(b, b_is_nk)
         self.a, self.b = a, b
         self.out = torch.empty(rows, n, dtype=dtype, device=a.device)
         layout = N.B_NK if b_is_nk else N.B_KN
+        self.transport = _resolve_transport(transport, RS_TRANSPORTS, "push", heap, "tp_rowwise")
         if world == 1:
             cfg = _base_config(N.MODE_PLAIN, dtype, m, n, k, 0, 1, layout, cta_group, block_n,
-                               group_m, num_sms)
+                               group_m, num_sms, fp32_mode=fp32_mode)
             cfg.out[0] = self.out.data_ptr()
         else:
             st_off, self.staging = heap.empty((2, world, rows, n), dtype)
             cfg = _base_config(N.MODE_RS, dtype, m, n, k, rank, world, layout, cta_group, block_n,
-                               group_m, num_sms, 0, chunk_rows)
+                               group_m, num_sms, chunk_rows, fp32_mode=fp32_mode,
+                               unrotated=unrotated)
+            cfg.rs_transport = RS_TRANSPORTS[self.transport]
             for p in range(world):
-                cfg.out[p] = heap.ptr(st_off, p)
+                cfg.stage[p] = heap.ptr(st_off, p)
+            if self.transport == "multimem":
+                cfg.mc_ptr = heap.mc_ptr(st_off)
             cfg.out[rank] = self.out.data_ptr()
-            cfg.stage_local = heap.ptr(st_off)
             self._alloc_signals(cfg)
         cfg.a, cfg.b = a.data_ptr(), b.data_ptr()
-        cfg.variant = int(variant)            # experimental A/B schedule variants (0 = production)
         if self.trace_buf is not None:
             cfg.trace = self.trace_buf.data_ptr()
         self.plan = TpGemmPlan(cfg, keepalive=(a, b, self.out))

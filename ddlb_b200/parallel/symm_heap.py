@@ -1,8 +1,8 @@
 """Symmetric heap: one device arena per rank, mapped into every peer.
 
 Native part: ``csrc/runtime.inl`` (``cudaMalloc`` arena exported with ``cudaIpc``,
-peer mapping, zeroed signal pads, device barrier kernel). The handle exchange is
-the only thing done through ``torch.distributed``. This replaces the NCCL
+peer mapping, zeroed signal pads, device barrier kernel). The handles travel through the
+communicator's key-value store (no NCCL communicator). This replaces the NCCL
 communicator set-up of the reference's implementations
 (``ddlb/primitives/TPColumnwise/pytorch.py:53-59``): the fused kernels address
 peer memory directly as ``base[peer] + offset``.
@@ -36,6 +36,8 @@ class _RawCudaBuffer:
 class SymmetricHeap:
     """Bump allocator over the symmetric arena; identical call sequence on every rank
     yields identical offsets, which is what makes ``base[peer] + offset`` valid."""
+
+    has_multicast = False       # the cudaIpc arena has no NVLS window (see vmm_heap.VmmHeap)
 
     def __init__(self, comm=None, min_bytes: int = 0, *, device: Optional[int] = None,
                  rank: Optional[int] = None, world: Optional[int] = None, exchange: bool = True):
@@ -100,6 +102,9 @@ class SymmetricHeap:
 
     def ptr(self, offset: int, rank: Optional[int] = None) -> int:
         return self.base(rank) + offset
+
+    def mc_ptr(self, offset: int) -> int:
+        raise N.NativeError("this heap has no multicast window (use DDLB_SYMM_MODE=vmm)")
 
     def tensor(self, offset: int, shape: Tuple[int, ...], dtype):
         """Torch view of LOCAL heap memory at ``offset`` (no copy, no ownership)."""

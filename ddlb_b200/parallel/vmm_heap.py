@@ -1,13 +1,20 @@
-"""EXPERIMENTAL symmetric heap on the CUDA virtual-memory API with an NVLS multicast window.
+"""Symmetric heap on the CUDA virtual-memory API with an NVLS multicast window.
 
 Drop-in for ``SymmetricHeap`` (same ``base/ptr/alloc/alloc_signals/tensor/empty/barrier``) plus
 ``mc_ptr(offset)``: an address whose stores reach every rank's copy (``multimem.st``) and whose
 ``multimem.ld_reduce`` loads return the sum over all ranks, computed in the NVSwitch. Native
 part: ``csrc/vmm_heap.inl``. The allocations are exchanged between the rank processes as POSIX
-file descriptors over Unix datagram sockets (``SCM_RIGHTS``).
+file descriptors over Unix datagram sockets (``SCM_RIGHTS``); everything else the set-up needs
+(socket names, "did every rank succeed") goes through the communicator's store, so no NCCL
+communicator is involved.
 
-Written after round 1's GPU budget was spent: never run on hardware. Select it with
-``DDLB_SYMM_MODE=vmm`` once ``tests/test_vmm_experimental_gpu.py`` has passed.
+This is what the reference reaches through nvFuser's ``cuda`` backend with
+``multicast_protocol=multimem`` (``ddlb/primitives/TPColumnwise/fuser.py:171-206``).
+
+Set-up is collective and all-or-nothing: if ANY rank cannot create its allocation, map a peer or
+join the multicast group, every rank raises ``VmmUnavailable`` (the communicator then falls back
+to the cudaIpc heap in ``DDLB_SYMM_MODE=auto``); a heap without a multicast window is still a
+valid heap (``has_multicast`` False, the ``multimem`` transports refuse it).
 """
 from __future__ import annotations
 
@@ -19,7 +26,11 @@ import uuid
 from typing import List, Optional
 
 from .. import _native as N
-from .symm_heap import SIGNAL_BYTES, SymmetricHeap, _ALIGN, _BARRIER_WORDS, _RawCudaBuffer
+from .symm_heap import SIGNAL_BYTES, SymmetricHeap, _BARRIER_WORDS
+
+
+class VmmUnavailable(RuntimeError):
+    """The VMM heap cannot be set up on this system (raised on every rank alike)."""
 
 
 class VmmHeap(SymmetricHeap):
@@ -31,37 +42,60 @@ class VmmHeap(SymmetricHeap):
         want = max(int(min_bytes), int(os.environ.get("DDLB_SYMM_HEAP_BYTES", "0")), 64 << 20) + 2 * SIGNAL_BYTES
         self._lib = N.lib()
         self._torch = torch
-        handle = ctypes.c_void_p()
-        N.check(self._lib.ddlb_vmm_create(self.device_index, self.rank, self.world, want,
-                                          ctypes.byref(handle)), "vmm_create")
-        self._h = handle
-        self.capacity = int(self._lib.ddlb_vmm_bytes(self._h))
-        self._cursor = SIGNAL_BYTES
-        self._sig_cursor = _BARRIER_WORDS * 4
+        self._h = None
         self._closed = False
         self._barrier_epoch = 0
         self.has_multicast = False
+        self._cursor = SIGNAL_BYTES
+        self._sig_cursor = _BARRIER_WORDS * 4
+
+        handle = ctypes.c_void_p()
+        err = ""
+        if self._lib.ddlb_vmm_create(self.device_index, self.rank, self.world, want,
+                                     ctypes.byref(handle)) != 0:
+            err = self._lib.ddlb_last_error().decode(errors="replace")
+        else:
+            self._h = handle
+        self._agree(err, "cuMemCreate")
+        self.capacity = int(self._lib.ddlb_vmm_bytes(self._h))
         if self.world > 1:
-            comm.init_process_group()
-            self._run_id = self._agree_run_id()
+            self._run_id = comm.all_gather_bytes(uuid.uuid4().hex.encode())[0].decode()
             self._map_peers()
-            if self._lib.ddlb_vmm_has_multicast(self._h):
-                self._setup_multicast()
+            want_mc = os.environ.get("DDLB_VMM_MULTICAST", "1") != "0"
+            mc_err = "" if (want_mc and self._lib.ddlb_vmm_has_multicast(self._h)) else "not supported"
+            if self._all_ok(mc_err):
+                # a failure from here on leaves a usable heap without the multicast window
+                self.has_multicast = self._all_ok(self._try(self._setup_multicast))
             self.barrier()
             torch.cuda.synchronize()
 
-    # ---------------------------------------------------------------- fd exchange
-    def _agree_run_id(self) -> str:
-        mine = uuid.uuid4().hex.encode()
-        return self.comm.all_gather_bytes(mine)[0].decode()
+    # ------------------------------------------------------- collective agreement
+    @staticmethod
+    def _try(fn) -> str:
+        try:
+            fn()
+            return ""
+        except Exception as exc:                     # noqa: BLE001 - reported to every rank
+            return f"{type(exc).__name__}: {exc}"[:300] or "error"
 
+    def _all_ok(self, err: str) -> bool:
+        if self.world == 1:
+            return not err
+        return not any(self.comm.all_gather_bytes(err.encode()[:300] or b"ok") [r] != b"ok"
+                       for r in range(self.world))
+
+    def _agree(self, err: str, what: str) -> None:
+        errs = [err] if self.world == 1 else [
+            b.decode(errors="replace") for b in self.comm.all_gather_bytes(err.encode()[:300] or b"ok")]
+        bad = [(r, e) for r, e in enumerate(errs) if e not in ("", "ok")]
+        if bad:
+            self.close()
+            raise VmmUnavailable(f"{what} failed on rank {bad[0][0]}: {bad[0][1]}")
+
+    # ---------------------------------------------------------------- fd exchange
     def _sock_path(self, tag: str, rank: int) -> str:
         base = os.path.dirname(os.environ.get("DDLB_RDZV_PREFIX", "")) or tempfile.gettempdir()
         return os.path.join(base, f"ddlb_fd_{self._run_id[:12]}_{tag}_{rank}.sock")
-
-    def _host_barrier(self) -> None:
-        import torch.distributed as dist
-        dist.barrier()
 
     def _exchange_fds(self, fd: Optional[int], tag: str, senders: List[int]) -> List[int]:
         """Every rank in ``senders`` sends ``fd`` to all other ranks; returns fds by sender."""
@@ -73,7 +107,7 @@ class VmmHeap(SymmetricHeap):
             pass
         rx.bind(path)
         rx.settimeout(120)
-        self._host_barrier()                         # every rank is bound
+        self.comm.host_barrier()                     # every rank is bound
         out = [-1] * self.world
         try:
             if self.rank in senders:
@@ -86,7 +120,7 @@ class VmmHeap(SymmetricHeap):
             for _ in range(expected):
                 msg, fds, _flags, _addr = socket.recv_fds(rx, 16, 1)
                 out[msg[0]] = fds[0]
-            self._host_barrier()
+            self.comm.host_barrier()
         finally:
             rx.close()
             try:
@@ -96,31 +130,48 @@ class VmmHeap(SymmetricHeap):
         return out
 
     def _map_peers(self) -> None:
+        """Collective: every failure is agreed on by all ranks before anyone raises."""
         fd = ctypes.c_int(-1)
-        N.check(self._lib.ddlb_vmm_export_fd(self._h, ctypes.byref(fd)), "vmm_export_fd")
+        err = ""
+        if self._lib.ddlb_vmm_export_fd(self._h, ctypes.byref(fd)) != 0:
+            err = self._lib.ddlb_last_error().decode(errors="replace")
+        self._agree(err, "cuMemExportToShareableHandle")
         fds = self._exchange_fds(fd.value, "mem", list(range(self.world)))
         for p, peer_fd in enumerate(fds):
             if p == self.rank:
                 continue
-            N.check(self._lib.ddlb_vmm_import_peer(self._h, p, peer_fd), f"vmm_import_peer({p})")
+            if not err and self._lib.ddlb_vmm_import_peer(self._h, p, peer_fd) != 0:
+                err = f"rank {p}: " + self._lib.ddlb_last_error().decode(errors="replace")
             os.close(peer_fd)
         os.close(fd.value)
+        self._agree(err, "mapping a peer allocation")
 
     def _setup_multicast(self) -> None:
         fd = ctypes.c_int(-1)
+        err = ""
         if self.rank == 0:
-            N.check(self._lib.ddlb_vmm_mc_create(self._h, ctypes.byref(fd)), "vmm_mc_create")
+            if self._lib.ddlb_vmm_mc_create(self._h, ctypes.byref(fd)) != 0:
+                err = self._lib.ddlb_last_error().decode(errors="replace")
+        if not self._all_ok(err):
+            raise N.NativeError(f"cuMulticastCreate: {err or 'failed on rank 0'}")
         fds = self._exchange_fds(fd.value if self.rank == 0 else None, "mc", [0])
+        err = ""
         if self.rank != 0:
-            N.check(self._lib.ddlb_vmm_mc_import(self._h, fds[0]), "vmm_mc_import")
+            if self._lib.ddlb_vmm_mc_import(self._h, fds[0]) != 0:
+                err = self._lib.ddlb_last_error().decode(errors="replace")
             os.close(fds[0])
         else:
             os.close(fd.value)
-        N.check(self._lib.ddlb_vmm_mc_add_device(self._h), "vmm_mc_add_device")
-        self._host_barrier()                         # every device added before anyone binds
-        N.check(self._lib.ddlb_vmm_mc_bind(self._h), "vmm_mc_bind")
-        self._host_barrier()
-        self.has_multicast = True
+        if not err and self._lib.ddlb_vmm_mc_add_device(self._h) != 0:
+            err = self._lib.ddlb_last_error().decode(errors="replace")
+        # every device must have been added before anyone binds (and nobody may bind if one failed)
+        if not self._all_ok(err):
+            raise N.NativeError(f"cuMulticastAddDevice: {err or 'failed on a peer'}")
+        err = ""
+        if self._lib.ddlb_vmm_mc_bind(self._h) != 0:
+            err = self._lib.ddlb_last_error().decode(errors="replace")
+        if not self._all_ok(err):
+            raise N.NativeError(f"cuMulticastBindMem: {err or 'failed on a peer'}")
 
     # ------------------------------------------------------------------ addresses
     def base(self, rank: Optional[int] = None) -> int:
@@ -130,7 +181,8 @@ class VmmHeap(SymmetricHeap):
         return int(ptr)
 
     def mc_ptr(self, offset: int) -> int:
-        ptr = self._lib.ddlb_vmm_mc_base(self._h)
+        """Multicast alias of ``offset``: ``multimem.*`` instructions only."""
+        ptr = self._lib.ddlb_vmm_mc_base(self._h) if self.has_multicast else None
         if not ptr:
             raise N.NativeError("no multicast window on this heap")
         return int(ptr) + offset
@@ -178,4 +230,6 @@ class VmmHeap(SymmetricHeap):
     def close(self) -> None:
         if not self._closed:
             self._closed = True
-            self._lib.ddlb_vmm_destroy(self._h)
+            if self._h is not None:
+                self._lib.ddlb_vmm_destroy(self._h)
+                self._h = None

@@ -1,8 +1,12 @@
-"""Reference implementation names served by the fused GEMM+ReduceScatter kernel
-(see ``ddlb_b200/primitives/TPColumnwise/compat.py`` for the policy).
+"""Reference implementation NAMES served by the fused GEMM+ReduceScatter kernel
+(see ``ddlb_b200/primitives/TPColumnwise/compat.py`` for the policy and the row labels).
 
 * ``fuser`` (reference ``TPRowwise/fuser.py:171-312``): ``algorithm`` / ``s`` map
-  one-to-one; the transport/stream options are accepted and recorded only.
+  one-to-one (``default`` and ``p2p_pipeline`` are the same ring schedule here, see
+  ``fused.py``); ``offset_stream_indexing_by_rank=False`` selects the un-rotated owner order;
+  with ``backend=cuda``, ``multicast_protocol=multimem`` selects ``multimem.ld_reduce`` and
+  ``memcpy`` / ``batch_memcpy`` the push transport. Other ``backend`` values and
+  ``inter_stream_synchronization`` are reported as ignored.
 * ``transformer_engine`` (reference ``TPRowwise/transformer_engine.py:66-79``):
   GEMM + reduce-scatter with sequence parallelism == ``default`` schedule.
 """
@@ -12,6 +16,7 @@ from .fused import FusedTPRowwise
 
 
 class _CompatRowwise(FusedTPRowwise):
+    SERVED_BY = "fused"
     COMPAT_DEFAULTS = {}
     COMPAT_ALLOWED = {}
     KERNEL_OPTIONS = FusedTPRowwise.DEFAULT_OPTIONS
@@ -23,7 +28,12 @@ class _CompatRowwise(FusedTPRowwise):
         self.compat_options = compat.as_dict()
         super().__init__(m, n, k, dtype=dtype, seed=seed, **self._translate(self.compat_options))
 
-    def _translate(self, opts):
+    @classmethod
+    def honoured_options(cls, options):
+        return set(options)
+
+    @classmethod
+    def _translate(cls, opts):
         return {}
 
 
@@ -44,12 +54,28 @@ class FuserTPRowwise(_CompatRowwise):
     DEFAULT_OPTIONS = dict(COMPAT_DEFAULTS)
     ALLOWED_VALUES = COMPAT_ALLOWED
 
-    def _translate(self, o):
-        return {"algorithm": o["algorithm"], "s": o["s"]}
+    @classmethod
+    def honoured_options(cls, options):
+        keep = {"algorithm", "offset_stream_indexing_by_rank"}
+        if options.get("algorithm") == "coll_pipeline":
+            keep.add("s")
+        if options.get("backend") == "cuda":
+            keep |= {"backend", "multicast_protocol"}
+        return keep
+
+    @classmethod
+    def _translate(cls, o):
+        transport = "auto"
+        if o["backend"] == "cuda":
+            transport = {"multimem": "multimem", "memcpy": "push",
+                         "batch_memcpy": "push"}.get(o["multicast_protocol"], "auto")
+        return {"algorithm": o["algorithm"], "s": o["s"],
+                "rank_rotate": bool(o["offset_stream_indexing_by_rank"]), "transport": transport}
 
 
 class TransformerEngineTPRowwise(_CompatRowwise):
     DEFAULT_OPTIONS = {}
 
-    def _translate(self, o):
+    @classmethod
+    def _translate(cls, o):
         return {"algorithm": "default"}

@@ -3,15 +3,20 @@ in ONE hand-written sm_100a kernel per rank (``csrc/tp_gemm_sm100.cuh``).
 
 Replaces cuBLAS + ``ncclReduceScatter`` (reference
 ``ddlb/primitives/TPRowwise/pytorch.py:70-85``) and the nvFuser pipelines
-(``ddlb/primitives/TPRowwise/fuser.py:15-169``). Partial-output tiles leave TMEM,
-are rounded once to the output type and stored with TMA straight into the owning
-rank's staging buffer over NVLink; the owner's own tiles are scheduled last and
-their epilogue adds the staged partials in fp32. No full ``[m,n]`` partial is ever
-written to local HBM and no separate reduction kernel runs.
+(``ddlb/primitives/TPRowwise/fuser.py:15-169``). Partial-output tiles leave TMEM, are
+rounded once to the output type and stored with 128-bit stores into a staging slot; the
+aux warps of every CTA of the owning rank sum the d slots in fp32 as soon as all of them
+have landed. No full ``[m,n]`` partial is ever written to local HBM by a separate GEMM and
+no separate reduction kernel runs.
 
-``algorithm``: ``default`` / ``p2p_pipeline`` visit owners in ring order
-(rank+1 ... rank) with one chunk per owner; ``coll_pipeline`` splits every
-owner's rows into ``s`` slabs and visits slab j of all owners before slab j+1.
+``algorithm``: ``default`` and ``p2p_pipeline`` are the SAME schedule here (owners visited
+ring-wise, one chunk per owner: that is what the reference's p2p pipeline does, and a
+non-overlapped "GEMM, then collective" order has no place in a fused kernel);
+``coll_pipeline`` splits every owner's rows into ``s`` slabs and visits slab j of all owners
+before slab j+1.
+``transport``: ``push`` (default/``auto``/``p2p``: partials go to the owner's staging, own
+tiles last), ``pull`` (partials stay local, owners load them over NVLink), ``multimem``
+(``multimem.ld_reduce``: the NVSwitch adds the d copies).
 """
 from __future__ import annotations
 
@@ -24,14 +29,18 @@ class FusedTPRowwise(TPRowwise):
         "s": 2,
         "cta_group": 0,
         "block_n": 0,
-        "transport": "p2p",
+        "transport": "auto",
+        "rank_rotate": True,
+        "fp32_mode": "3xtf32",
     }
     ALLOWED_VALUES = {
         "algorithm": ["default", "coll_pipeline", "p2p_pipeline"],
         "s": (1, 1024),
         "cta_group": [0, 1, 2],
         "block_n": [0, 128, 256],
-        "transport": ["auto", "p2p"],
+        "transport": ["auto", "p2p", "push", "pull", "multimem"],
+        "rank_rotate": [True, False],
+        "fp32_mode": ["3xtf32", "tf32"],
     }
 
     def __init__(self, *args, **kwargs):
@@ -42,12 +51,9 @@ class FusedTPRowwise(TPRowwise):
         comm = self.communicator
         if not comm.is_cuda:
             raise RuntimeError("the fused implementation needs a CUDA device (sm_100a)")
-        from ...ops.tp_gemm import tf32_enabled
-        ok_dtypes = (torch.float16, torch.bfloat16) + ((torch.float32,) if tf32_enabled() else ())
-        if self.torch_dtype not in ok_dtypes:
+        if self.torch_dtype not in (torch.float16, torch.bfloat16, torch.float32):
             raise ValueError(
-                f"fused tp_rowwise supports float16/bfloat16 (got {self.dtype}); float32 through "
-                "kind::tf32 is opt-in (DDLB_ENABLE_TF32=1) until validated on hardware; "
+                f"fused tp_rowwise supports float16/bfloat16/float32 (got {self.dtype}); "
                 "use the pytorch baseline for other dtypes")
         d = comm.world_size
         rows = self.m // d
@@ -59,12 +65,12 @@ class FusedTPRowwise(TPRowwise):
             chunk_rows = rows // s
         heap = None
         if d > 1:
-            comm.init_process_group()
             heap = comm.symmetric_heap(2 * self.m * self.n * self.A.element_size() + (64 << 20))
         self.op = FusedGemmReduceScatter(
             heap, comm.rank, d, self.m, self.n, self.k, self.torch_dtype, self.A, self.B,
             chunk_rows=chunk_rows, cta_group=int(self.options["cta_group"]),
-            block_n=int(self.options["block_n"]))
+            block_n=int(self.options["block_n"]), transport=self.options["transport"],
+            fp32_mode=self.options["fp32_mode"], unrotated=not self.options["rank_rotate"])
         torch.cuda.synchronize()
         if d > 1:
             heap.barrier()

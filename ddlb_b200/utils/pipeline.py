@@ -6,14 +6,12 @@ device input (copy stream), run the primitive (compute stream), read one result 
 back to pinned host memory. ``depth`` instances of the primitive rotate so the copy
 for step ``i`` can run while step ``i-1`` computes.
 
-Why ``depth >= 3`` for multi-rank AllGather->GEMM: the input shard of an instance is
-read by the PEERS' kernels (they gather it over NVLink), and a peer may lag. The
-kernel of step ``j+1`` on this rank cannot finish before every peer has started its
-own step ``j+1`` kernel, i.e. finished step ``j`` (the fused kernels wait for the
-peers' "ready" flags). So the input used by step ``j`` may be overwritten once THIS
-rank's step ``j+1`` kernel has completed; the copy for step ``i`` (same slot as step
-``i - depth``) therefore waits for the completion of step ``i - depth + 1``. With
-``depth = 3`` that is step ``i-2``, which leaves step ``i-1`` free to overlap.
+Why ``depth = 2`` is enough, also for multi-rank AllGather->GEMM: the input shard of an
+instance is read by the PEERS' kernels (they gather it over NVLink), but the fused kernel
+returns only after every peer has finished reading it (closing handshake in
+``csrc/tp_gemm_sm100.cuh``), exactly like ``ncclAllGather`` and its send buffer. The copy for
+step ``i`` (same slot as step ``i - depth``) therefore waits for THIS rank's step
+``i - depth`` kernel and nothing else.
 """
 from __future__ import annotations
 
@@ -21,15 +19,13 @@ from typing import Callable, List, Optional
 
 
 class PipelinedRunner:
-    def __init__(self, impl_factory: Callable[[], object], depth: int = 3):
+    def __init__(self, impl_factory: Callable[[], object], depth: int = 2):
         import torch
         if depth < 1:
             raise ValueError("depth must be >= 1")
         self.depth = depth
         self.impls: List[object] = [impl_factory() for _ in range(depth)]
         self.comm = self.impls[0].communicator
-        if self.comm.world_size > 1 and depth < 3:
-            raise ValueError("multi-rank pipelining needs depth >= 3 (see module docstring)")
         self.copy_stream = torch.cuda.Stream()
         self._done: List[Optional[object]] = []      # event per step: kernel finished
         self._step = 0
@@ -44,8 +40,8 @@ class PipelinedRunner:
         i = self._step
         impl = self.impls[i % self.depth]
         compute = torch.cuda.current_stream()
-        # the slot's previous user was step i-depth; safe once step i-depth+1 has finished
-        guard = i - self.depth + 1
+        # the slot's previous user was step i-depth: wait for that kernel
+        guard = i - self.depth
         if guard >= 0 and guard < len(self._done):
             self.copy_stream.wait_event(self._done[guard])
         with torch.cuda.stream(self.copy_stream):

@@ -79,16 +79,31 @@ int ddlb_vmm_destroy(ddlb_vmm* s);
 
 /* --------------------------------------------------------------- fused GEMM */
 enum { DDLB_MODE_PLAIN = 0, DDLB_MODE_AG_BEFORE = 1, DDLB_MODE_AG_AFTER = 2, DDLB_MODE_RS = 3 };
-/* F32: fp32 inputs and outputs computed with kind::tf32 tensor-core MMAs (fp32 accumulate);
- * written after round 1's GPU budget was spent, not yet validated on hardware */
+/* F32: fp32 inputs and outputs on the tensor cores. Default 3xTF32 (hi/lo split of both
+ * operands, three kind::tf32 MMAs per k-step, ~fp32 accuracy); DDLB_FP32_TF32 runs the single
+ * pass (10-bit mantissa inputs). fp32 needs B as [n,k] (DDLB_B_ROW_MAJOR_NK). */
 enum { DDLB_DTYPE_F16 = 0, DDLB_DTYPE_BF16 = 1, DDLB_DTYPE_F32 = 2 };
+enum { DDLB_FP32_3XTF32 = 0, DDLB_FP32_TF32 = 1 };
 enum { DDLB_B_ROW_MAJOR_KN = 0, DDLB_B_ROW_MAJOR_NK = 1 };
-/* who moves the A shards in AG_BEFORE. EVERY_CTA (default): two warps of every CTA push the
- * own shard to all peers with 128-bit loads/stores from registers. EVERY_CTA_TMA: one warp
- * of every CTA pulls 8 KiB pieces with bulk-async copies through shared memory. PULL_CTAS /
- * PUSH_CTAS: n_comm_ctas dedicated CTAs with bulk-async copies. */
-enum { DDLB_COMM_EVERY_CTA = 0, DDLB_COMM_PULL_CTAS = 1, DDLB_COMM_PUSH_CTAS = 2,
-       DDLB_COMM_EVERY_CTA_TMA = 3, DDLB_COMM_EVERY_CTA_PULL = 4 /* register path, pulling */ };
+/* Who moves the A shards in AG_BEFORE (aux warps of every CTA, 128-bit accesses through
+ * registers). PULL (default): read the peers' shards, write the local gathered buffer.
+ * PUSH: read the own shard once, write it into every peer's gathered buffer.
+ * PUSH_MULTICAST: one multimem.st per 16 bytes, replicated by the NVSwitch (needs mc_ptr).
+ * Reference counterparts: ncclAllGather (TPColumnwise/pytorch.py:96), nvFuser's p2p / multicast
+ * protocols (TPColumnwise/fuser.py:171-206). */
+enum { DDLB_AG_PULL = 0, DDLB_AG_PUSH = 1, DDLB_AG_PUSH_MULTICAST = 2 };
+/* How AG_AFTER's epilogue writes a C tile into every rank's C: TMA stores to all d ranks,
+ * 128-bit stores to the peers (+ TMA locally), or one multimem.st (needs mc_ptr). */
+enum { DDLB_EPI_TMA = 0, DDLB_EPI_ST128 = 1, DDLB_EPI_MULTICAST = 2 };
+/* RS: PUSH partial tiles into the owner's staging and let the owner sum its local slots;
+ * PULL: keep them in the local staging, the owner loads all d copies over NVLink;
+ * PULL_MULTICAST: the owner issues multimem.ld_reduce, the NVSwitch adds the d copies
+ * (needs mc_ptr). Reference counterparts: ncclReduceScatter (TPRowwise/pytorch.py:83),
+ * nvFuser p2p pipeline and multimem protocol (TPRowwise/fuser.py:116-169,186-197). */
+enum { DDLB_RS_PUSH = 0, DDLB_RS_PULL = 1, DDLB_RS_PULL_MULTICAST = 2 };
+/* activation fused into the epilogue (no reference counterpart: the reference has no model
+ * code; used by ddlb_b200.models.TPMLP so that the block needs no elementwise kernel) */
+enum { DDLB_ACT_NONE = 0, DDLB_ACT_RELU = 1, DDLB_ACT_SILU = 2, DDLB_ACT_GELU_TANH = 3 };
 
 typedef struct ddlb_tp_gemm_config {
   int32_t mode;          /* DDLB_MODE_* */
@@ -98,34 +113,36 @@ typedef struct ddlb_tp_gemm_config {
   int32_t block_n;       /* 128 or 256, 0 = auto */
   int32_t group_m;       /* rasterisation group, 0 = auto */
   int32_t num_sms;       /* CTAs to launch, 0 = all SMs */
-  int32_t n_comm_ctas;   /* AG_BEFORE: CTAs that pull peer shards, 0 = auto */
   int32_t rank, world;
   int32_t chunk_rows;    /* rows per pipeline chunk inside a shard, 0 = auto */
-  int32_t comm_transport; /* AG_BEFORE: DDLB_COMM_* */
+  int32_t ag_transport;  /* AG_BEFORE: DDLB_AG_* */
+  int32_t epi_transport; /* AG_AFTER: DDLB_EPI_* */
+  int32_t rs_transport;  /* RS: DDLB_RS_* */
+  int32_t unrotated;     /* 1: shards are visited 0..d-1 on every rank instead of starting at the
+                          * own / next rank (nvFuser offset_stream_indexing_by_rank=False,
+                          * TPColumnwise/fuser.py:165,250) */
+  int32_t fp32_mode;     /* DDLB_FP32_* */
+  int32_t epilogue_act;  /* DDLB_ACT_*: applied to the fp32 accumulator before the output is
+                          * rounded (PLAIN / AG_*; not on tp_rowwise partial sums) */
   int64_t m, n, k;       /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
   /* PLAIN:     a = A[m,k]                 out[rank] = C[m,n]
    * AG_BEFORE: a = gathered A[m,k] (own shard rows already in place), peer_a[r] = rank r's
-   *            gathered buffer, out[rank] = C[m,n]
-   * AG_AFTER:  a = A_local[m/d,k]         out[r] = rank r's C[m,n]
+   *            gathered buffer, out[rank] = C[m,n]; mc_ptr = multicast alias of the gathered A
+   * AG_AFTER:  a = A_local[m/d,k]         out[r] = rank r's C[m,n]; mc_ptr = alias of C
    * RS:        a = A_local[m,k/d], b = B_local[k/d,n], out[rank] = C_shard[m/d,n],
-   *            out[r != rank] = rank r's staging [2][d][m/d][n], stage_local = own staging */
+   *            stage[r] = rank r's staging [2][d][m/d][n]; mc_ptr = alias of the staging */
   void* a;
   void* b;
   void* out[DDLB_MAX_WORLD];
   void* peer_a[DDLB_MAX_WORLD];
-  void* stage_local;
+  void* stage[DDLB_MAX_WORLD];
+  void* mc_ptr;
   uint32_t* sig_local;                  /* this op's signal words (zero-initialised) */
   uint32_t* sig_peer[DDLB_MAX_WORLD];   /* the same block on every peer */
   /* optional device trace buffer (NULL = off): grid * DDLB_TRACE_ROLES * DDLB_TRACE_SLOTS
    * records of 16 bytes {tag, arg, time_lo, time_hi (globaltimer ns)}, zero-initialised by the
    * caller. Only for fp16/bf16, cta_group 2, block_n 256, B [k,n]. No reference counterpart. */
   void* trace;
-  /* experimental schedule variant (0 = production kernel). RS: bit 0 announces a pushed tile
-   * immediately, bit 1 loads two staged partials at a time, bit 2 (RS and AG_AFTER) pushes tiles
-   * to peers with 128-bit stores instead of TMA stores. Values 1, 2, 3, 4, 6. Flagship
-   * configuration only. */
-  int32_t variant;
-  int32_t reserved;
 } ddlb_tp_gemm_config;
 #define DDLB_TRACE_ROLES 4
 #define DDLB_TRACE_SLOTS 128
@@ -137,7 +154,7 @@ int64_t ddlb_tp_gemm_sig_words(const ddlb_tp_gemm_config* cfg);
 int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_plan** out);
 /* epoch: 1, 2, 3, ... incremented by the caller on every launch, identical on all ranks */
 int ddlb_tp_gemm_run(ddlb_tp_gemm_plan* plan, uint32_t epoch, void* stream);
-/* resolved launch shape: {grid, cluster, smem_bytes, cta_group, block_n, stages, n_comm_ctas,
+/* resolved launch shape: {grid, cluster, smem_bytes, cta_group, block_n, stages, threads,
  * chunk_rows}; */
 int ddlb_tp_gemm_info(const ddlb_tp_gemm_plan* plan, int32_t out[8]);
 int ddlb_tp_gemm_destroy(ddlb_tp_gemm_plan* plan);
@@ -156,7 +173,9 @@ int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, uint32_t epo
  * must never take an allocator lock. It calls no cudaMalloc / cudaFree / pool routine.
  *  - world > DDLB_EMULATED_STATIC_MAX_WORLD is refused with an error.
  *  - The first call on each device looks up the array's device address (with that device
- *    current); make that first call outside any stream capture.
+ *    current); make that first call before any stream capture begins. The per-device address
+ *    cache is a plain array: two host threads making the first call on one device at the same
+ *    time both store the same value, which is harmless.
  *  - All calls share the one array. Each call rewrites every block it uses, so nothing
  *    has to be cleared beforehand; but two calls whose work overlaps on the GPU (different
  *    streams, same device) overwrite each other's blocks: keep calls on one stream, or
@@ -168,7 +187,7 @@ int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int world, uint3
 
 /* Introspection of the tile schedule on the host (no GPU needed when cfg->num_sms > 0): the
  * resolved launch/schedule parameters {num_m_blocks, num_n_blocks, mblks_per_part, chunk_mblks,
- * group_m, tile_m, block_n, cta_group, chunk_rows, n_comm_ctas, grid, comm_in_cta}, and the
+ * group_m, tile_m, block_n, cta_group, chunk_rows, part0, grid, threads}, and the
  * kernel's own tile_coord() evaluated for tiles [first, first+count). No reference counterpart. */
 int ddlb_debug_schedule(const ddlb_tp_gemm_config* cfg, int32_t out[12]);
 int ddlb_debug_tile_coords(const ddlb_tp_gemm_config* cfg, int32_t first, int32_t count, int32_t* out);

@@ -41,6 +41,7 @@ def main():
     ap.add_argument("--shapes", default="256x256x64,256x512x256,384x320x200,4096x1024x1024,65536x1024x1024")
     ap.add_argument("--dtypes", default="bfloat16,float16")
     ap.add_argument("--perf", action="store_true")
+    ap.add_argument("--fp32-mode", default="3xtf32", choices=["3xtf32", "tf32"])
     args = ap.parse_args()
     torch.manual_seed(0)
     ok_all = True
@@ -53,7 +54,8 @@ def main():
             b = b_kn.t().contiguous() if args.b_layout == "nk" else b_kn
             try:
                 plan, out = plain_gemm_plan(a, b, b_is_nk=args.b_layout == "nk",
-                                            cta_group=args.cta_group, block_n=args.block_n)
+                                            cta_group=args.cta_group, block_n=args.block_n,
+                                            fp32_mode=args.fp32_mode)
             except Exception as exc:
                 print(f"[{dt_name} {shp}] plan failed: {exc}")
                 ok_all = False
@@ -61,7 +63,8 @@ def main():
             out.fill_(float("nan"))
             plan.run()
             torch.cuda.synchronize()
-            ref = a.float() @ b_kn.float()
+            torch.backends.cuda.matmul.allow_tf32 = False
+            ref = (a.double() @ b_kn.double()).float() if dt == torch.float32 else a.float() @ b_kn.float()
             err = (out.float() - ref).abs()
             tol = 2e-2 * (k ** 0.5) + 1e-2 * ref.abs()
             bad = int((~(err <= tol)).sum())
@@ -78,6 +81,11 @@ def main():
                 fl = 2.0 * m * n * k / 1e9
                 line += (f" | ours {t_med*1e3:.1f}us ({fl/t_med:.0f} TF, best {fl/t_min:.0f})"
                          f" cublas {t_ref*1e3:.1f}us ({fl/t_ref:.0f} TF, best {fl/t_ref_min:.0f})")
+                if dt == torch.float32:
+                    torch.backends.cuda.matmul.allow_tf32 = True
+                    t_tf, _ = bench(lambda: torch.matmul(a, b_kn))
+                    torch.backends.cuda.matmul.allow_tf32 = False
+                    line += f" cublas(allow_tf32) {t_tf*1e3:.1f}us ({fl/t_tf:.0f} TF)"
             print(line, flush=True)
     sys.exit(0 if ok_all else 1)
 

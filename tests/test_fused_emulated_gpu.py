@@ -27,14 +27,13 @@ def _inputs(world, m, n, k, dtype, rowwise):
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-@pytest.mark.parametrize("order,chunk_rows,transport", [
-    ("AG_before", 0, "cta"), ("AG_before", 256, "cta"), ("AG_before", -1, "cta"),
-    ("AG_before", 0, "cta_tma"), ("AG_before", 256, "cta_tma"),
-    ("AG_before", 0, "cta_pull"), ("AG_before", 256, "cta_pull"),
-    ("AG_before", 0, "pull"), ("AG_before", 256, "pull"),
-    ("AG_before", 0, "push"), ("AG_before", 256, "push"), ("AG_after", 0, "cta")])
+@pytest.mark.parametrize("order,chunk_rows,transport,unrotated", [
+    ("AG_before", 0, "pull", False), ("AG_before", 256, "pull", False), ("AG_before", -1, "pull", False),
+    ("AG_before", 0, "pull", True), ("AG_before", 256, "pull", True),
+    ("AG_before", 0, "push", False), ("AG_before", 256, "push", False), ("AG_before", -1, "push", True),
+    ("AG_after", 0, "tma", False), ("AG_after", 0, "st128", False)])
 @pytest.mark.parametrize("cta_group", [1, 2])
-def test_allgather_gemm_emulated(world, order, chunk_rows, transport, cta_group):
+def test_allgather_gemm_emulated(world, order, chunk_rows, transport, unrotated, cta_group):
     import torch
     from ddlb_b200.ops.emulation import make_emulated_heaps, run_emulated
     from ddlb_b200.ops.tp_gemm import FusedAllGatherGemm
@@ -44,8 +43,8 @@ def test_allgather_gemm_emulated(world, order, chunk_rows, transport, cta_group)
     a, b, ref = _inputs(world, m, n, k, dtype, False)
     heaps = make_emulated_heaps(world, 2 * m * max(k, 2 * n) * 2 + (8 << 20))
     ops = [FusedAllGatherGemm(heaps[r], r, world, m, n, k, a.dtype, b, order=order,
-                              chunk_rows=cr, n_comm_ctas=2 * cta_group, cta_group=cta_group,
-                              transport=transport)
+                              chunk_rows=cr, cta_group=cta_group, transport=transport,
+                              unrotated=unrotated)
            for r in range(world)]
     for r, op in enumerate(ops):
         op.a_shard.copy_(a[r * rows:(r + 1) * rows])
@@ -64,7 +63,7 @@ def test_allgather_gemm_emulated(world, order, chunk_rows, transport, cta_group)
             if order == "AG_before" and epoch < 3:
                 # wipe the gathered rows of the peers: the next launch must fetch them again
                 keep = op.a_shard.clone()
-                op.a_gathered.zero_()
+                op.a_gathered.fill_(float("nan"))
                 op.a_shard.copy_(keep)
         torch.cuda.synchronize()
     for op in ops:
@@ -76,8 +75,10 @@ def test_allgather_gemm_emulated(world, order, chunk_rows, transport, cta_group)
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("chunk_rows", [0, 256])
 @pytest.mark.parametrize("cta_group", [1, 2])
-@pytest.mark.parametrize("dtype", ["bfloat16", "float16"])
-def test_gemm_reduce_scatter_emulated(world, chunk_rows, cta_group, dtype):
+@pytest.mark.parametrize("dtype,transport,unrotated", [
+    ("bfloat16", "push", False), ("float16", "push", False), ("float16", "push", True),
+    ("bfloat16", "pull", False), ("float16", "pull", False)])
+def test_gemm_reduce_scatter_emulated(world, chunk_rows, cta_group, dtype, transport, unrotated):
     import torch
     from ddlb_b200.ops.emulation import make_emulated_heaps, run_emulated
     from ddlb_b200.ops.tp_gemm import FusedGemmReduceScatter
@@ -88,15 +89,47 @@ def test_gemm_reduce_scatter_emulated(world, chunk_rows, cta_group, dtype):
     a_sh = [a[:, r * kk:(r + 1) * kk].contiguous() for r in range(world)]
     b_sh = [b[r * kk:(r + 1) * kk].contiguous() for r in range(world)]
     ops = [FusedGemmReduceScatter(heaps[r], r, world, m, n, k, a.dtype, a_sh[r], b_sh[r],
-                                  chunk_rows=chunk_rows, cta_group=cta_group)
+                                  chunk_rows=chunk_rows, cta_group=cta_group, transport=transport,
+                                  unrotated=unrotated)
            for r in range(world)]
     for epoch in (1, 2, 3, 4):                              # both staging parities, twice
+        for op in ops:
+            op.out.fill_(float("nan"))
+            # a partial that is summed before it has landed must not pass: poison the staging
+            # half this epoch writes (the other half may still be read by nobody: launches of
+            # one stream are serialised)
+            op.staging[epoch & 1].fill_(float("nan"))
+        torch.cuda.synchronize()
+        run_emulated([op.plan for op in ops], epoch)
+        torch.cuda.synchronize()
+        for r, op in enumerate(ops):
+            _tol_check(op.out, ref[r * rows:(r + 1) * rows], k, f"RS rank {r} epoch {epoch}")
+    for op in ops:
+        op.close()
+    for h in heaps:
+        h.close()
+
+
+@pytest.mark.parametrize("n", [448, 320])
+def test_reduce_scatter_n_not_multiple_of_block_n(n):
+    """The reducers' units overhang N when an n-block does: those lanes must stay idle."""
+    import torch
+    from ddlb_b200.ops.emulation import make_emulated_heaps, run_emulated
+    from ddlb_b200.ops.tp_gemm import FusedGemmReduceScatter
+    world, m, k = 2, 512, 256
+    rows, kk = m // world, k // world
+    a, b, ref = _inputs(world, m, n, k, "bfloat16", True)
+    heaps = make_emulated_heaps(world, 4 * m * n * 2 + (8 << 20))
+    ops = [FusedGemmReduceScatter(heaps[r], r, world, m, n, k, a.dtype,
+                                  a[:, r * kk:(r + 1) * kk].contiguous(),
+                                  b[r * kk:(r + 1) * kk].contiguous()) for r in range(world)]
+    for epoch in (1, 2):
         for op in ops:
             op.out.fill_(float("nan"))
         run_emulated([op.plan for op in ops], epoch)
         torch.cuda.synchronize()
         for r, op in enumerate(ops):
-            _tol_check(op.out, ref[r * rows:(r + 1) * rows], k, f"RS rank {r} epoch {epoch}")
+            _tol_check(op.out, ref[r * rows:(r + 1) * rows], k, f"RS n={n} rank {r} epoch {epoch}")
     for op in ops:
         op.close()
     for h in heaps:

@@ -81,9 +81,42 @@ def test_compat_option_tables_match_reference_names():
         "multicast_protocol", "inter_stream_synchronization"]
     assert "order" not in FuserTPRowwise.DEFAULT_OPTIONS
     assert FuserTPColumnwise.ALLOWED_VALUES["algorithm"] == ["default", "coll_pipeline", "p2p_pipeline"]
-    inst = FuserTPColumnwise.__new__(FuserTPColumnwise)
-    assert inst._translate({**FuserTPColumnwise.DEFAULT_OPTIONS, "algorithm": "coll_pipeline", "s": 4}) == {
-        "order": "AG_before", "algorithm": "coll_pipeline", "s": 4}
+    assert FuserTPColumnwise._translate(
+        {**FuserTPColumnwise.DEFAULT_OPTIONS, "algorithm": "coll_pipeline", "s": 4}) == {
+        "order": "AG_before", "algorithm": "coll_pipeline", "s": 4, "rank_rotate": True,
+        "transport": "auto"}
+    # nvFuser's symmetric-memory backend: the multicast protocol selects the data path, and the
+    # un-rotated stream order the un-rotated shard order
+    cuda = {**FuserTPColumnwise.DEFAULT_OPTIONS, "backend": "cuda", "multicast_protocol": "multimem",
+            "offset_stream_indexing_by_rank": False}
+    assert FuserTPColumnwise._translate(cuda)["transport"] == "multimem"
+    assert FuserTPColumnwise._translate(cuda)["rank_rotate"] is False
+    assert FuserTPColumnwise._translate({**cuda, "multicast_protocol": "memcpy"})["transport"] == "push"
+    assert FuserTPRowwise._translate({**FuserTPRowwise.DEFAULT_OPTIONS, "backend": "cuda",
+                                      "multicast_protocol": "multimem"})["transport"] == "multimem"
+
+
+def test_compat_rows_are_labelled_as_served_by_the_fused_kernel():
+    from ddlb_b200.benchmark import _merged_options, describe_implementation
+    from ddlb_b200.primitives.TPColumnwise.compat import (FuserTPColumnwise,
+                                                           TransformerEngineTPColumnwise)
+    from ddlb_b200.primitives.TPColumnwise.fused import FusedTPColumnwise
+    opts = _merged_options(FuserTPColumnwise, {"backend": "nccl", "algorithm": "coll_pipeline", "s": 4,
+                                               "inter_stream_synchronization": True})
+    label, option = describe_implementation(FuserTPColumnwise, "fuser", opts)
+    assert label.startswith("fused[as fuser] (") and "backend" not in label
+    assert "algorithm=coll_pipeline" in label and "s=4" in label
+    assert "ignored: " in option and "backend=nccl" in option.split("ignored: ")[1]
+    assert "inter_stream_synchronization=True" in option.split("ignored: ")[1]
+    label, option = describe_implementation(
+        FuserTPColumnwise, "fuser", _merged_options(FuserTPColumnwise, {"backend": "cuda",
+                                                                        "multicast_protocol": "multimem"}))
+    assert "multicast_protocol=multimem" in label and "backend=cuda" in label
+    label, _ = describe_implementation(TransformerEngineTPColumnwise, "transformer_engine", {})
+    assert label == "fused[as transformer_engine]"
+    label, option = describe_implementation(FusedTPColumnwise, "fused",
+                                            _merged_options(FusedTPColumnwise, {}))
+    assert label.startswith("fused (") and "ignored" not in option
 
 
 def test_roofline_arithmetic(monkeypatch, tmp_path):

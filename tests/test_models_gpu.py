@@ -1,17 +1,22 @@
-"""TP MLP block (AllGather->GEMM, activation, GEMM->ReduceScatter) on one GPU: world=1 through
-the fused kernels, and two emulated ranks, against a PyTorch fp32 reference."""
+"""TP MLP block (AllGather->GEMM with the activation fused into its epilogue, GEMM->ReduceScatter)
+on one GPU: world=1 through the fused kernels, and two emulated ranks, against a PyTorch fp32
+reference."""
 import pytest
 
 pytestmark = pytest.mark.gpu
 
 
-def _reference(x, w_up, w_down):
+def _reference(x, w_up, w_down, act="silu"):
     import torch
-    h = torch.nn.functional.silu((x.float() @ w_up.float()).to(x.dtype).float()).to(x.dtype)
+    pre = x.float() @ w_up.float()                       # the kernel activates the fp32 accumulator
+    fn = {"silu": torch.nn.functional.silu, "relu": torch.relu,
+          "gelu_tanh": lambda t: torch.nn.functional.gelu(t, approximate="tanh")}[act]
+    h = fn(pre).to(x.dtype)
     return h.float() @ w_down.float()
 
 
-def test_tp_mlp_single_rank():
+@pytest.mark.parametrize("act", ["silu", "relu", "gelu_tanh"])
+def test_tp_mlp_single_rank(act):
     import torch
     from ddlb_b200.models import TPMLP
     torch.manual_seed(5)
@@ -19,10 +24,10 @@ def test_tp_mlp_single_rank():
     x = torch.randn(tokens, hidden, device="cuda", dtype=dt) * 0.5
     w_up = torch.randn(hidden, ffn, device="cuda", dtype=dt) * 0.1
     w_down = torch.randn(ffn, hidden, device="cuda", dtype=dt) * 0.1
-    mlp = TPMLP(None, 0, 1, tokens, hidden, ffn, dt, w_up, w_down)
+    mlp = TPMLP(None, 0, 1, tokens, hidden, ffn, dt, w_up, w_down, activation=act)
     y = mlp(x)
     torch.cuda.synchronize()
-    ref = _reference(x, w_up, w_down)
+    ref = _reference(x, w_up, w_down, act)
     torch.testing.assert_close(y.float(), ref, rtol=3e-2, atol=3e-2 * ref.abs().max().item())
     assert mlp.gpu_launches == 2
     mlp.close()
@@ -47,9 +52,7 @@ def test_tp_mlp_two_emulated_ranks():
     torch.cuda.synchronize()
     # the ranks of one emulated launch must run together: drive the two phases by hand
     run_emulated([m.up.plan for m in mlps], 1)
-    for m in mlps:
-        m._h.copy_(m.activation(m.up.out[0]))
-    run_emulated([m.down.plan for m in mlps], 1)
+    run_emulated([m.down.plan for m in mlps], 1)      # H went straight from one kernel to the next
     torch.cuda.synchronize()
     ref = _reference(x, w_up, w_down)
     for r, m in enumerate(mlps):

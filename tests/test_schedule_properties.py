@@ -17,9 +17,12 @@ MODES = {"plain": N.MODE_PLAIN, "ag_before": N.MODE_AG_BEFORE, "ag_after": N.MOD
          "rs": N.MODE_RS}
 
 
-def _cfg(mode, world, rank, m, n, k, cta_group=0, block_n=0, group_m=0, chunk_rows=0, dtype=N.DTYPE_BF16):
+def _cfg(mode, world, rank, m, n, k, cta_group=0, block_n=0, group_m=0, chunk_rows=0, dtype=N.DTYPE_BF16,
+         rs_transport=N.RS_PUSH, unrotated=False):
     cfg = N.TpGemmConfig()
-    cfg.mode, cfg.dtype, cfg.b_layout = MODES[mode], dtype, N.B_KN
+    # fp32 operands are K-major for the tensor cores: B is [n,k]
+    cfg.mode, cfg.dtype, cfg.b_layout = MODES[mode], dtype, (N.B_NK if dtype == N.DTYPE_F32 else N.B_KN)
+    cfg.rs_transport, cfg.unrotated = rs_transport, int(unrotated)
     cfg.cta_group, cfg.block_n, cfg.group_m, cfg.num_sms = cta_group, block_n, group_m, 148
     cfg.rank, cfg.world, cfg.chunk_rows = rank, world, chunk_rows
     cfg.m, cfg.n, cfg.k = m, n, k
@@ -33,7 +36,7 @@ def _schedule(cfg):
     if rc != 0:
         raise N.NativeError(lib.ddlb_last_error().decode())
     keys = ("num_m_blocks", "num_n_blocks", "mblks_per_part", "chunk_mblks", "group_m", "tile_m",
-            "block_n", "cta_group", "chunk_rows", "n_comm_ctas", "grid", "comm_in_cta")
+            "block_n", "cta_group", "chunk_rows", "part0", "grid", "threads")
     return dict(zip(keys, list(out)))
 
 
@@ -54,6 +57,8 @@ shape_strategy = st.tuples(
     st.sampled_from([0, 128, 256]),                      # block_n
     st.sampled_from([0, 1, 3, 8, 16]),                   # group_m
     st.integers(0, 6),                                   # chunk selector
+    st.sampled_from(["push", "pull", "multimem"]),       # tp_rowwise transport
+    st.booleans(),                                       # un-rotated shard order
     st.data(),
 )
 
@@ -61,7 +66,7 @@ shape_strategy = st.tuples(
 @settings(max_examples=300, deadline=None, suppress_health_check=[HealthCheck.too_slow])
 @given(shape_strategy)
 def test_every_tile_once_and_rows_belong_to_their_part(args):
-    mode, world, mult, n64, g, bn, group_m, chunk_sel, data = args
+    mode, world, mult, n64, g, bn, group_m, chunk_sel, rs_t, unrot, data = args
     if mode == "plain":
         world = 1
     rank = data.draw(st.integers(0, world - 1))
@@ -74,7 +79,8 @@ def test_every_tile_once_and_rows_belong_to_their_part(args):
         divisors = [d for d in range(1, mult + 1) if mult % d == 0]
         chunk_rows = divisors[chunk_sel % len(divisors)] * tile_m
     cfg = _cfg(mode, world, rank, m, n, k, cta_group=g, block_n=bn, group_m=group_m,
-               chunk_rows=chunk_rows)
+               chunk_rows=chunk_rows, unrotated=unrot,
+               rs_transport={"push": N.RS_PUSH, "pull": N.RS_PULL, "multimem": N.RS_PULL_MULTICAST}[rs_t])
     sched = _schedule(cfg)
     tiles = _tiles(cfg, sched)
     nm, nn = sched["num_m_blocks"], sched["num_n_blocks"]
@@ -92,16 +98,22 @@ def test_every_tile_once_and_rows_belong_to_their_part(args):
         first_seen = {}
         for idx, (m_blk, n_blk, part, chunk) in enumerate(tiles):
             first_seen.setdefault((chunk, part), idx)
-        rot0 = 1 if mode == "rs" else 0
+        # first shard: AG the own one (already here), RS push the next rank (own last, its
+        # partials need no NVLink); pull reductions and the un-rotated order start at 0
+        if unrot or (mode == "rs" and rs_t != "push"):
+            part0 = 0
+        else:
+            part0 = (rank + (1 if mode == "rs" else 0)) % world
+        assert sched["part0"] == part0
         order = sorted(first_seen, key=first_seen.get)
-        expected = [(c, (rank + rot0 + pi) % world) for c in range(per_part // cm) for pi in range(world)]
+        expected = [(c, (part0 + pi) % world) for c in range(per_part // cm) for pi in range(world)]
         # grouped rasterisation interleaves tiles of neighbouring chunks, but the first
         # appearance of each (chunk, part) follows the communication order
         assert order == expected
-        if mode == "rs":
+        if not unrot and mode == "rs" and rs_t == "push":
             # the rank's own rows are the last part of every stage
             assert [p for (c, p) in expected if c == 0][-1] == rank
-        else:
+        elif not unrot and mode == "ag_before":
             assert expected[0][1] == rank                           # own rows first
     else:
         assert all(t[2] == rank and t[3] == 0 for t in tiles)
@@ -111,7 +123,7 @@ def test_headline_configs_resolve_as_documented():
     s = _schedule(_cfg("ag_before", 8, 3, 65536, 1024, 1024))
     assert (s["cta_group"], s["block_n"], s["tile_m"]) == (2, 256, 256)
     assert s["chunk_rows"] == 512                     # ~1 MiB of bf16 A per chunk at k = 1024
-    assert s["comm_in_cta"] == 2 or s["comm_in_cta"] in (0, 1, 2, 3)
+    assert s["threads"] == 384                        # aux warps 8..11 carry the all-gather
     assert s["num_m_blocks"] == 256 and s["num_n_blocks"] == 4 and s["grid"] == 148
     s = _schedule(_cfg("rs", 8, 0, 8192, 1024, 8192, dtype=N.DTYPE_F16))
     assert s["mblks_per_part"] == 4 and s["chunk_mblks"] == 4       # one chunk per owner by default
@@ -133,10 +145,12 @@ def test_bad_configs_are_rejected_with_a_reason(kwargs, needle):
 
 
 def test_fp32_geometry_resolves():
-    s = _schedule(_cfg("plain", 1, 0, 512, 96, 36, dtype=N.DTYPE_F32))   # n % 32, k % 4 suffice
-    assert s["num_n_blocks"] == 1
-    with pytest.raises(N.NativeError, match="multiple of 32"):
-        _schedule(_cfg("plain", 1, 0, 512, 80, 36, dtype=N.DTYPE_F32))
+    s = _schedule(_cfg("plain", 1, 0, 512, 96, 36, dtype=N.DTYPE_F32))   # n % 4, k % 4 suffice for [n,k]
+    assert s["num_n_blocks"] == 1 and s["threads"] == 384                # 3xTF32 split warps
+    cfg = _cfg("plain", 1, 0, 512, 96, 36, dtype=N.DTYPE_F32)
+    cfg.b_layout = N.B_KN
+    with pytest.raises(N.NativeError, match=r"\[n,k\]"):
+        _schedule(cfg)
 
 
 @settings(max_examples=150, deadline=None, suppress_health_check=[HealthCheck.too_slow])

@@ -1,5 +1,6 @@
-"""VMM heap + NVLS multicast window (two real GPUs). Never run on hardware in round 1: opt-in
-(``DDLB_RUN_EXPERIMENTAL=1``)."""
+"""VMM heap + NVLS multicast window on two real GPUs: peer mapping through POSIX file
+descriptors, ``multimem.st`` / ``multimem.ld_reduce`` round trip, and the fused kernels'
+``multimem`` transports against the fp32 reference."""
 import os
 import subprocess
 import sys
@@ -7,13 +8,18 @@ import textwrap
 
 import pytest
 
-pytestmark = [pytest.mark.gpu, pytest.mark.multigpu,
-              pytest.mark.skipif(os.environ.get("DDLB_RUN_EXPERIMENTAL", "0") != "1",
-                                 reason="experimental: set DDLB_RUN_EXPERIMENTAL=1")]
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+def _need_two_gpus():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 CUDA devices")
+
+
 def test_vmm_heap_peer_mapping_and_multicast(tmp_path):
+    _need_two_gpus()
     script = tmp_path / "vmm.py"
     script.write_text(textwrap.dedent(f'''
         import sys
@@ -22,7 +28,6 @@ def test_vmm_heap_peer_mapping_and_multicast(tmp_path):
         from ddlb_b200.communicator import Communicator
         from ddlb_b200.parallel.vmm_heap import VmmHeap
         comm = Communicator()
-        comm.init_process_group()
         heap = VmmHeap(comm, 64 << 20)
         off, t = heap.empty((1024,), torch.float32)
         t.fill_(float(comm.rank + 1))

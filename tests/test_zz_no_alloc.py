@@ -5,8 +5,11 @@ the library instead of a per-call ``cudaMallocAsync``.
 
 The entry point is called straight through the C ABI (ctypes) and its results are compared
 with those of the allocating entry point ``ddlb_tp_gemm_run_emulated`` on the same plans,
-twice in a row, because the shared scratch keeps the previous call's contents. Kept in a
-file that pytest collects last so a ``-x`` run has exercised everything else first.
+twice in a row. The scratch is shared by every call and keeps what the last call left in it,
+so between the two calls a DIFFERENT set of plans (other shape, four ranks instead of two)
+goes through the same entry point: the second call must not see any of that. The amount of
+free device memory is sampled around the calls to check the claim in the name. Kept in a file
+that pytest collects last so a ``-x`` run has exercised everything else first.
 """
 import ctypes
 
@@ -49,7 +52,26 @@ def test_static_scratch_entry_point_matches_allocating_one():
         bad, worst = _within_tolerance(expected[r], exact[r * rows:(r + 1) * rows], k)
         assert bad == 0, f"allocating entry point wrong on rank {r}: max err {worst}"
 
-    # new entry point, two calls in a row on the shared static scratch
+    # a second, different job for the same scratch: 4 ranks, another shape
+    world2, m2, n2, k2 = 4, 2048, 256, 1024
+    rows2, kk2 = m2 // world2, k2 // world2
+    a2 = torch.randn(m2, k2, device="cuda", dtype=torch.float16)
+    b2 = torch.randn(k2, n2, device="cuda", dtype=torch.float16)
+    exact2 = a2.float() @ b2.float()
+    heaps2 = make_emulated_heaps(world2, 32 << 20)
+    ops2 = [FusedGemmReduceScatter(heaps2[r], r, world2, m2, n2, k2, a2.dtype,
+                                   a2[:, r * kk2:(r + 1) * kk2].contiguous(),
+                                   b2[r * kk2:(r + 1) * kk2].contiguous()) for r in range(world2)]
+    plans2 = (ctypes.c_void_p * world2)(*[op.plan._h for op in ops2])
+    # first use on this device looks the scratch address up; do it before sampling memory
+    N.check(lib.ddlb_tp_gemm_run_emulated_static(plans2, world2, 1, stream), "run_emulated_static")
+    torch.cuda.synchronize()
+    for r in range(world2):
+        bad, worst = _within_tolerance(ops2[r].out, exact2[r * rows2:(r + 1) * rows2], k2)
+        assert bad == 0, f"static entry point, other job, rank {r}: max err {worst}"
+
+    # new entry point, two calls in a row on the shared static scratch, the other job in between
+    free_before = torch.cuda.mem_get_info()[0]
     for epoch in (2, 3):
         for op in ops:
             op.out.fill_(float("nan"))
@@ -59,6 +81,13 @@ def test_static_scratch_entry_point_matches_allocating_one():
         for r in range(world):
             bad, worst = _within_tolerance(ops[r].out, expected[r], k)
             assert bad == 0, f"call with epoch {epoch}, rank {r}: {bad} elements off, max err {worst}"
+        if epoch == 2:
+            N.check(lib.ddlb_tp_gemm_run_emulated_static(plans2, world2, 2, stream),
+                    "run_emulated_static")
+            torch.cuda.synchronize()
+    # nothing was taken from (or returned to) the device between the samples: the fills above
+    # write existing tensors and the entry point itself allocates nothing
+    assert torch.cuda.mem_get_info()[0] == free_before
 
     # more ranks than the fixed scratch holds: refused, with a message that says so
     too_many = (ctypes.c_void_p * 9)(*([ops[0].plan._h] * 9))
@@ -67,7 +96,7 @@ def test_static_scratch_entry_point_matches_allocating_one():
     message = lib.ddlb_last_error().decode()
     assert "exceeds" in message and "8" in message
 
-    for op in ops:
+    for op in ops + ops2:
         op.close()
-    for h in heaps:
+    for h in heaps + heaps2:
         h.close()
