@@ -81,8 +81,8 @@ class VmmHeap(SymmetricHeap):
     def _all_ok(self, err: str) -> bool:
         if self.world == 1:
             return not err
-        return not any(self.comm.all_gather_bytes(err.encode()[:300] or b"ok") [r] != b"ok"
-                       for r in range(self.world))
+        answers = self.comm.all_gather_bytes(err.encode()[:300] or b"ok")
+        return all(a == b"ok" for a in answers)
 
     def _agree(self, err: str, what: str) -> None:
         errs = [err] if self.world == 1 else [

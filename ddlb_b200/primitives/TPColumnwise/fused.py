@@ -107,6 +107,20 @@ class FusedTPColumnwise(TPColumnwise):
             return rows // s
         return 0
 
+    def poison(self) -> None:
+        import torch
+        op, comm = self.op, self.communicator
+        if comm.world_size > 1:
+            if op.a_gathered is not None:                # AG_before: the peers' rows
+                keep = op.a_shard.clone()
+                op.a_gathered.fill_(float("nan"))
+                op.a_shard.copy_(keep)
+            comm.symmetric_heap().barrier()              # peers' pushes must not precede the fill
+        for out in op.out:
+            out.fill_(float("nan"))
+        if comm.world_size > 1:
+            comm.symmetric_heap().barrier()
+
     def run(self):
         return self.op.run()
 

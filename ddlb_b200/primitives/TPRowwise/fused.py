@@ -76,6 +76,13 @@ class FusedTPRowwise(TPRowwise):
             heap.barrier()
             torch.cuda.synchronize()
 
+    def poison(self) -> None:
+        op, comm = self.op, self.communicator
+        op.out.fill_(float("nan"))
+        if comm.world_size > 1:
+            op.staging.fill_(float("nan"))               # both parities: nobody is mid-launch here
+            comm.symmetric_heap().barrier()              # peers' pushes must not precede the fill
+
     def run(self):
         return self.op.run()
 

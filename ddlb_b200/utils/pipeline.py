@@ -2,9 +2,11 @@
 input overlapped with the current step's kernel.
 
 Each step: copy this rank's input shard from pinned host memory into the primitive's
-device input (copy stream), run the primitive (compute stream), read one result row
-back to pinned host memory. ``depth`` instances of the primitive rotate so the copy
-for step ``i`` can run while step ``i-1`` computes.
+device input (copy stream), run the primitive (compute stream), read the result (or a
+row slice of it) back to pinned host memory (read stream). ``depth`` instances of the
+primitive rotate so the copy for step ``i`` and the read-back of step ``i-2`` can run
+while step ``i-1`` computes; PCIe is full duplex, so a step costs
+``max(H2D, kernel, D2H)`` instead of their sum.
 
 Why ``depth = 2`` is enough, also for multi-rank AllGather->GEMM: the input shard of an
 instance is read by the PEERS' kernels (they gather it over NVLink), but the fused kernel
@@ -26,37 +28,54 @@ class PipelinedRunner:
         self.depth = depth
         self.impls: List[object] = [impl_factory() for _ in range(depth)]
         self.comm = self.impls[0].communicator
-        self.copy_stream = torch.cuda.Stream()
+        self.copy_stream = torch.cuda.Stream()       # host -> device
+        self.read_stream = torch.cuda.Stream()       # device -> host
         self._done: List[Optional[object]] = []      # event per step: kernel finished
+        self._read: List[Optional[object]] = []      # event per step: result read back
         self._step = 0
         first = self.impls[0]
         self.input_shape = tuple(first.A.shape)
         self.input_dtype = first.A.dtype
 
-    def step(self, host_in, host_out=None):
-        """One end-to-end step. ``host_in``: pinned tensor shaped like the rank's input
-        shard. ``host_out``: optional pinned 1-D tensor receiving row 0 of the result."""
+    def step(self, host_in, host_out=None, rows: Optional[slice] = None):
+        """One end-to-end step. ``host_in``: pinned tensor shaped like the rank's input shard.
+        ``host_out``: optional pinned tensor receiving ``result[rows]`` (default: row 0)."""
         import torch
         i = self._step
         impl = self.impls[i % self.depth]
         compute = torch.cuda.current_stream()
-        # the slot's previous user was step i-depth: wait for that kernel
-        guard = i - self.depth
-        if guard >= 0 and guard < len(self._done):
-            self.copy_stream.wait_event(self._done[guard])
+        prev = i - self.depth                        # the slot's previous user
+        if 0 <= prev < len(self._done):
+            self.copy_stream.wait_event(self._done[prev])     # its kernel has read the input
         with torch.cuda.stream(self.copy_stream):
             impl.A.copy_(host_in, non_blocking=True)
             copied = torch.cuda.Event()
             copied.record(self.copy_stream)
         compute.wait_event(copied)
+        if 0 <= prev < len(self._read) and self._read[prev] is not None:
+            compute.wait_event(self._read[prev])              # its result has left the device
         out = impl.run()
         done = torch.cuda.Event()
         done.record(compute)
         self._done.append(done)
+        read = None
         if host_out is not None:
-            host_out.copy_(out[0], non_blocking=True)
+            self.read_stream.wait_event(done)
+            with torch.cuda.stream(self.read_stream):
+                host_out.copy_(out[rows] if rows is not None else out[0], non_blocking=True)
+                read = torch.cuda.Event()
+                read.record(self.read_stream)
+        self._read.append(read)
         self._step += 1
         return out
+
+    def drain(self) -> None:
+        """Make the current stream wait for every copy issued so far (end of a timed region)."""
+        import torch
+        compute = torch.cuda.current_stream()
+        for ev in self._read[-self.depth:]:
+            if ev is not None:
+                compute.wait_event(ev)
 
     @property
     def gpu_launches(self) -> int:
@@ -69,3 +88,4 @@ class PipelinedRunner:
             impl.close()
         self.impls = []
         self._done = []
+        self._read = []

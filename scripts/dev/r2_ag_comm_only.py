@@ -1,7 +1,8 @@
 #!/usr/bin/env python3
-"""Round-2 experiment: how fast is the AllGather inside the fused kernel when the GEMM is
-negligible (n = 64) compared with the headline n = 1024? Separates "copy path" from
-"contention with the GEMM's L2 traffic" (ROADMAP section 2). Launch with the in-tree launcher."""
+"""How fast is the AllGather inside the fused kernel when the GEMM is negligible (n = 64)
+compared with the headline n = 1024, for every transport and order? Separates "copy path" from
+"contention with the GEMM's L2 traffic". Launch with the in-tree launcher:
+    python -m ddlb_b200.launcher -np 2 scripts/dev/r2_ag_comm_only.py"""
 import os
 import sys
 
@@ -12,36 +13,44 @@ from ddlb_b200.communicator import Communicator  # noqa: E402
 from ddlb_b200.ops.tp_gemm import FusedAllGatherGemm  # noqa: E402
 
 
+def timed(comm, heap, op, iters=20):
+    torch.cuda.synchronize()
+    heap.barrier()
+    for _ in range(5):
+        op.run()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(iters)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(iters)]
+    for i in range(iters):
+        heap.barrier()
+        starts[i].record()
+        op.run()
+        ends[i].record()
+    torch.cuda.synchronize()
+    times = sorted(comm.all_reduce_max([s.elapsed_time(e) for s, e in zip(starts, ends)]))
+    return times[len(times) // 2], times[0]
+
+
 def main():
     m, k, dt = 65536, 1024, torch.bfloat16
     comm = Communicator()
-    comm.init_process_group()
     heap = comm.symmetric_heap(3 << 30)
     d, r = comm.world_size, comm.rank
-    moved = (d - 1) / d * m * k * 2
+    mc = getattr(heap, "has_multicast", False)
+    if r == 0:
+        print(f"world {d} heap {type(heap).__name__} multicast {mc}", flush=True)
     for n in (64, 1024):
         b = torch.randn(k, n, device=comm.device, dtype=dt)
-        for transport in ("cta_pull", "cta", "cta_tma"):
-            op = FusedAllGatherGemm(heap, r, d, m, n, k, dt, b, transport=transport)
+        cases = [("AG_before", t) for t in ["pull", "push"] + (["multimem"] if mc else [])]
+        cases += [("AG_after", t) for t in ["tma", "st128"] + (["multimem"] if mc else [])]
+        for order, transport in cases:
+            moved = (d - 1) / d * m * (k if order == "AG_before" else n) * 2
+            op = FusedAllGatherGemm(heap, r, d, m, n, k, dt, b, order=order, transport=transport)
             op.a_shard.normal_()
-            torch.cuda.synchronize()
-            heap.barrier()
-            for _ in range(5):
-                op.run()
-            iters = 20
-            starts = [torch.cuda.Event(enable_timing=True) for _ in range(iters)]
-            ends = [torch.cuda.Event(enable_timing=True) for _ in range(iters)]
-            for i in range(iters):
-                heap.barrier()
-                starts[i].record()
-                op.run()
-                ends[i].record()
-            torch.cuda.synchronize()
-            times = sorted(comm.all_reduce_max([s.elapsed_time(e) for s, e in zip(starts, ends)]))
+            med, best = timed(comm, heap, op)
             if r == 0:
-                med = times[len(times) // 2]
-                print(f"n={n:5d} transport={transport:8s} median {med * 1e3:7.1f} us  "
-                      f"gather rate {moved / (med * 1e6):6.1f} GB/s  info={op.plan.info}", flush=True)
+                print(f"n={n:5d} {order:9s} transport={transport:8s} median {med * 1e3:7.1f} us (best "
+                      f"{best * 1e3:7.1f})  inbound {moved / (med * 1e6):6.1f} GB/s  info={op.plan.info}",
+                      flush=True)
             op.close()
     comm.shutdown()
 

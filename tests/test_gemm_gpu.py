@@ -58,4 +58,12 @@ def test_unsupported_shapes_fail_loudly():
     with pytest.raises(NativeError):
         plain_gemm_plan(a, b)
     with pytest.raises(TypeError):
-        plain_gemm_plan(a.float(), b.float())
+        plain_gemm_plan(a.double(), b.double())
+    # float32 is served (3xTF32) through the [n,k] operand layout; a raw [k,n] config is refused
+    from ddlb_b200 import _native as N
+    import ctypes
+    cfg = N.TpGemmConfig()
+    cfg.mode, cfg.dtype, cfg.b_layout, cfg.world = N.MODE_PLAIN, N.DTYPE_F32, N.B_KN, 1
+    cfg.m, cfg.n, cfg.k = 128, 128, 64
+    assert N.lib().ddlb_tp_gemm_sig_words(ctypes.byref(cfg)) < 0
+    assert "[n,k]" in N.lib().ddlb_last_error().decode()

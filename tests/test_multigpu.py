@@ -1,5 +1,9 @@
-"""Real multi-GPU runs (cudaIpc symmetric heap, NVLink P2P, device barrier, fused kernels)
-through the public entry points, one process per GPU via the in-tree launcher."""
+"""Real multi-GPU runs (symmetric heap, NVLink P2P, device barrier, fused kernels) through the
+public entry points, one process per GPU via the in-tree launcher.
+
+Validation in the harness happens on an extra launch whose wire-fed buffers were overwritten
+with NaN first (``TPPrimitive.poison``) and uses the strict per-element tolerance, so a tile
+that is consumed before it arrived cannot pass on the previous launch's identical bytes."""
 import csv
 import json
 import os
@@ -39,10 +43,13 @@ def test_columnwise_fused_vs_nccl(world, tmp_path):
         "implementations": {
             "fused": [{"order": ["AG_before", "AG_after"]},
                       {"order": "AG_before", "algorithm": "coll_pipeline", "s": 2},
-                      {"order": "AG_before", "algorithm": "p2p_pipeline"}],
+                      {"order": "AG_before", "algorithm": "p2p_pipeline"},
+                      {"order": "AG_before", "transport": "push"},
+                      {"order": "AG_before", "rank_rotate": False},
+                      {"order": "AG_after", "transport": "st128"}],
             "pytorch": [{"backend": "nccl", "order": "AG_before"}]}}}
     rows = _launch(world, cfg, tmp_path)
-    assert len(rows) == 5
+    assert len(rows) == 8
     for r in rows:
         assert r["valid"] == "True" and r["error"] == "", r
         assert int(r["world_size"]) == world
@@ -57,9 +64,55 @@ def test_rowwise_fused_vs_nccl(world, tmp_path):
         "validate": True, "num_iterations": 10, "num_warmups": 3,
         "time_measurement_backend": "cuda_event", "output_csv": str(tmp_path / "out.csv"),
         "implementations": {
-            "fused": [{"algorithm": "default"}, {"algorithm": "coll_pipeline", "s": 2}],
+            "fused": [{"algorithm": "default"}, {"algorithm": "coll_pipeline", "s": 2},
+                      {"transport": "pull"}, {"rank_rotate": False}],
             "pytorch": [{"backend": "nccl"}]}}}
     rows = _launch(world, cfg, tmp_path)
-    assert len(rows) == 3
+    assert len(rows) == 5
     for r in rows:
         assert r["valid"] == "True" and r["error"] == "", r
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_float32_fused_both_primitives(world, tmp_path):
+    """The reference's default dtype on the fused path (3xTF32), real ranks."""
+    if _ngpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    for prim, k in (("tp_columnwise", 1024), ("tp_rowwise", 2048)):
+        cfg = {"benchmark": {
+            "primitive": prim, "m": 4096, "n": 512, "k": k, "dtype": "float32",
+            "validate": True, "num_iterations": 5, "num_warmups": 2,
+            "time_measurement_backend": "cuda_event", "output_csv": str(tmp_path / f"{prim}.csv"),
+            "implementations": {"fused": [{}], "pytorch": [{"backend": "nccl"}]}}}
+        rows = _launch(world, cfg, tmp_path)
+        assert len(rows) == 2
+        for r in rows:
+            assert r["valid"] == "True" and r["error"] == "", r
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_slow_rank_and_changing_inputs(world, tmp_path):
+    """One rank sleeps before some launches (no deadlock, no stale-flag consumption) and the
+    inputs change between launches (a premature read of a peer's shard would be wrong data,
+    not identical data). SURVEY section 4 item 4."""
+    if _ngpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    script = os.path.join(ROOT, "tests", "helpers", "slow_rank.py")
+    proc = subprocess.run([sys.executable, "-m", "ddlb_b200.launcher", "-np", str(world), "--timeout",
+                           "300", "--all-output", script], cwd=ROOT, capture_output=True, text=True,
+                          timeout=400)
+    assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
+    assert proc.stdout.count("slow-rank ok") == world
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_barrier_stress_epoch_wrap(world, tmp_path):
+    """10 000 device barriers back to back, starting just below the 32-bit epoch wrap."""
+    if _ngpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    script = os.path.join(ROOT, "tests", "helpers", "barrier_stress.py")
+    proc = subprocess.run([sys.executable, "-m", "ddlb_b200.launcher", "-np", str(world), "--timeout",
+                           "300", "--all-output", script], cwd=ROOT, capture_output=True, text=True,
+                          timeout=400)
+    assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
+    assert proc.stdout.count("barrier stress ok") == world

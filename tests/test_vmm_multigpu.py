@@ -47,3 +47,34 @@ def test_vmm_heap_peer_mapping_and_multicast(tmp_path):
                           timeout=180)
     assert proc.returncode == 0, proc.stdout[-2000:] + proc.stderr[-2000:]
     assert proc.stdout.count("peers ok") == 2
+
+
+def test_fused_multimem_transports_two_ranks(tmp_path):
+    """Both primitives through ``run_benchmark`` with the NVLS data paths: ``multimem.st`` all-gather
+    (both orders) and ``multimem.ld_reduce`` reduce-scatter, validated on a poisoned launch."""
+    _need_two_gpus()
+    import csv
+    import json
+    env = dict(os.environ, DDLB_SYMM_MODE="vmm")
+    for prim, impls in (
+            ("tp_columnwise", {"fused": [{"order": ["AG_before", "AG_after"], "transport": "multimem"}],
+                               "fuser": [{"backend": "cuda", "multicast_protocol": "multimem"}]}),
+            ("tp_rowwise", {"fused": [{"transport": "multimem"}],
+                            "fuser": [{"backend": "cuda", "multicast_protocol": "multimem"}]})):
+        out_csv = tmp_path / f"{prim}.csv"
+        cfg = {"benchmark": {"primitive": prim, "m": 8192, "n": 1024, "k": 2048, "dtype": "bfloat16",
+                             "validate": True, "num_iterations": 10, "num_warmups": 3,
+                             "time_measurement_backend": "cuda_event", "output_csv": str(out_csv),
+                             "implementations": impls}}
+        cfg_path = tmp_path / f"{prim}.json"
+        cfg_path.write_text(json.dumps(cfg))
+        proc = subprocess.run([sys.executable, "-m", "ddlb_b200.launcher", "-np", "2", "--timeout", "300",
+                               os.path.join(ROOT, "scripts", "run_benchmark.py"), str(cfg_path)],
+                              cwd=ROOT, capture_output=True, text=True, timeout=400, env=env)
+        assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
+        rows = list(csv.DictReader(open(out_csv)))
+        assert len(rows) == (3 if prim == "tp_columnwise" else 2)
+        for r in rows:
+            assert r["valid"] == "True" and r["error"] == "", r
+        assert any(r["implementation"].startswith("fused[as fuser]") and
+                   "multicast_protocol=multimem" in r["implementation"] for r in rows)
