@@ -189,15 +189,31 @@ __device__ __forceinline__ void red_add_release_gpu(uint32_t* p, uint32_t v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_relaxed_gpu(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
 // Spin until *p >= target (wrap-safe signed compare), system or gpu scope.
+// The poll is a RELAXED load and the acquire is ONE fence after the flag has been seen: an
+// acquire load compiles to LDG.STRONG + CCTL.IVALL, and a spinning warp then invalidates its
+// SM's whole L1 on every poll - with a producer lane spinning on every SM that throttled the
+// peer loads of the comm warps (round 2: the in-kernel all-gather ran at ~390 GB/s where a
+// plain copy kernel moves 620-740 GB/s).
 template <bool kSys>
 __device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t target) {
   uint64_t t0 = 0;
   uint32_t spins = 0;
   while (true) {
-    uint32_t v = kSys ? ld_acquire_sys(p) : ld_acquire_gpu(p);
-    if (static_cast<int32_t>(v - target) >= 0) return;
-    __nanosleep(32);
+    uint32_t v = kSys ? ld_relaxed_sys(p) : ld_relaxed_gpu(p);
+    if (static_cast<int32_t>(v - target) >= 0) break;
+    __nanosleep(64);
     if ((++spins & 0xfffu) == 0) {
       uint64_t now = globaltimer_ns();
       if (t0 == 0) t0 = now;
@@ -205,6 +221,7 @@ __device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t target)
         die(kErrFlagTimeout, static_cast<uint32_t>(reinterpret_cast<uintptr_t>(p)), target);
     }
   }
+  if (kSys) fence_acq_rel_sys(); else fence_acq_rel_gpu();
 }
 
 // ---------------------------------------------------------------------------

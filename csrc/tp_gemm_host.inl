@@ -254,6 +254,7 @@ static void fill_schedule(TpGemmParams& p, const ddlb_tp_gemm_config& c, const R
   p.epi_transport = c.epi_transport;
   p.rs_transport = c.rs_transport;
   p.act = c.epilogue_act;
+  p.comm_warps = c.comm_warps;
 }
 }  // namespace ddlb
 
@@ -554,6 +555,28 @@ extern "C" int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int w
     (void)cudaGetLastError();
     return set_error("emulated launch failed: %s", cudaGetErrorString(e));
   }
+  return 0;
+}
+
+// How many clusters of `cluster_size` CTAs of the flagship kernel (cta_group 2, BLOCK_N 256,
+// full shared memory) can be resident at once on the current device. Clusters must sit inside
+// one GPC, so 148 SMs do not always yield 148 / cluster_size clusters; this number decides
+// whether operand multicast across more than one CTA pair can pay. No reference counterpart.
+extern "C" int ddlb_max_active_clusters(int cluster_size, int threads, int* out) {
+  using namespace ddlb;
+  if (out == nullptr || cluster_size < 1 || cluster_size > 16) return set_error("bad arguments");
+  using Cfg = TpGemmCfg<2, 256>;
+  auto k = tp_gemm_kernel<2, 256, true>;
+  DDLB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  DDLB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+  int dev = 0, sms = 0;
+  DDLB_CUDA(cudaGetDevice(&dev));
+  DDLB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  cudaLaunchConfig_t lc;
+  cudaLaunchAttribute attr[1];
+  fill_launch(lc, attr, static_cast<unsigned>(sms - sms % cluster_size), threads, Cfg::kSmemBytes,
+              cluster_size, nullptr);
+  DDLB_CUDA(cudaOccupancyMaxActiveClusters(out, reinterpret_cast<const void*>(k), &lc));
   return 0;
 }
 

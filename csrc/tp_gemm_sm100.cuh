@@ -87,6 +87,7 @@ struct TpGemmParams {
   int act;                // epilogue activation on the final output (PLAIN / AG_*): kAct*
   // AG_BEFORE
   int ag_transport;
+  int comm_warps;                     // aux warps per CTA that move data (0 = all of them)
   const uint8_t* peer_a[kMaxWorld];   // every rank's gathered-A buffer (peer mapped)
   uint8_t* local_a;                   // this rank's gathered-A buffer
   uint32_t chunk_bytes;               // bytes of one chunk (chunk rows * K * elem)
@@ -411,6 +412,72 @@ __device__ __forceinline__ void store_chunk_st128(uint8_t* dst_base, size_t pitc
   }
 }
 
+// Sum the d staged copies of this lane's share of one unit (8 row groups x 16 bytes) and write
+// the result. kGroups row groups of all d sources are loaded before the first add (up to 16
+// independent 16-byte loads in flight per lane). ONE instantiation on purpose: several inlined
+// (or called) variants make ptxas spill kilobytes in a kernel at its 168-register cap.
+// push: the d partials sit in the local staging slots [parity][src];
+// pull: in slot [parity][rank] of every rank's staging (peer loads).
+template <int kSrc, int kGroups>
+__device__ __forceinline__ void rs_sum_unit(const TpGemmParams& p, uint32_t parity, size_t slot_bytes,
+                                            size_t pitch, int row0, int r_in, int colb, uint8_t* out,
+                                            bool bf16) {
+  const bool pull = p.rs_transport == kRsPull;
+#pragma unroll 1
+  for (int it0 = 0; it0 < 8; it0 += kGroups) {
+    uint4 raw[kSrc][kGroups];
+#pragma unroll
+    for (int s = 0; s < kSrc; ++s) {
+      if (s < p.world) {
+        const uint8_t* src = pull
+            ? p.stage_base[s] + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes
+            : p.stage_base[p.rank] + (static_cast<size_t>(parity) * p.world + s) * slot_bytes;
+#pragma unroll
+        for (int t = 0; t < kGroups; ++t) {
+          const size_t o = static_cast<size_t>(row0 + (it0 + t) * 4 + r_in) * pitch + colb;
+          raw[s][t] = __ldcg(reinterpret_cast<const uint4*>(src + o));
+        }
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < kGroups; ++t) {
+      uint4 res;
+      if (p.elem == 4) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int s = 0; s < kSrc; ++s) {
+          if (s < p.world) {
+            acc.x += __uint_as_float(raw[s][t].x);
+            acc.y += __uint_as_float(raw[s][t].y);
+            acc.z += __uint_as_float(raw[s][t].z);
+            acc.w += __uint_as_float(raw[s][t].w);
+          }
+        }
+        res = make_uint4(__float_as_uint(acc.x), __float_as_uint(acc.y), __float_as_uint(acc.z),
+                         __float_as_uint(acc.w));
+      } else {
+        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int s = 0; s < kSrc; ++s) {
+          if (s < p.world) {
+            const uint32_t w[4] = {raw[s][t].x, raw[s][t].y, raw[s][t].z, raw[s][t].w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float2 f = unpack2(w[i], bf16);
+              acc[2 * i] += f.x;
+              acc[2 * i + 1] += f.y;
+            }
+          }
+        }
+        res = make_uint4(pack2(acc[0], acc[1], bf16), pack2(acc[2], acc[3], bf16),
+                         pack2(acc[4], acc[5], bf16), pack2(acc[6], acc[7], bf16));
+      }
+      const size_t o = static_cast<size_t>(row0 + (it0 + t) * 4 + r_in) * pitch + colb;
+      st_global_v4(out + o, res);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------
 // RS: the reducers. The own shard [part_rows, N] is cut into units of 32 rows x 128 bytes
 // (the epilogue's staging granule). Unit u belongs to counter tile u / units_per_tile; a
@@ -464,62 +531,7 @@ __device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, 
         st_global_v4(out + o, v[it]);
       }
     } else {
-    // push: the d partials sit in the local staging slots [parity][src];
-    // pull: in slot [parity][rank] of every rank's staging (peer loads)
-    const bool pull = p.rs_transport == kRsPull;
-#pragma unroll 1
-    for (int it0 = 0; it0 < 8; it0 += 2) {
-      uint4 raw[kMaxWorld][2];
-#pragma unroll
-      for (int s = 0; s < kMaxWorld; ++s) {
-        if (s < p.world) {
-          const uint8_t* src = pull
-              ? p.stage_base[s] + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes
-              : p.stage_base[p.rank] + (static_cast<size_t>(parity) * p.world + s) * slot_bytes;
-#pragma unroll
-          for (int t = 0; t < 2; ++t) {
-            const size_t o = static_cast<size_t>(row0 + (it0 + t) * 4 + r_in) * pitch + colb;
-            raw[s][t] = __ldcg(reinterpret_cast<const uint4*>(src + o));
-          }
-        }
-      }
-#pragma unroll
-      for (int t = 0; t < 2; ++t) {
-        uint4 res;
-        if (p.elem == 4) {
-          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-          for (int s = 0; s < kMaxWorld; ++s) {
-            if (s < p.world) {
-              acc.x += __uint_as_float(raw[s][t].x);
-              acc.y += __uint_as_float(raw[s][t].y);
-              acc.z += __uint_as_float(raw[s][t].z);
-              acc.w += __uint_as_float(raw[s][t].w);
-            }
-          }
-          res = make_uint4(__float_as_uint(acc.x), __float_as_uint(acc.y), __float_as_uint(acc.z),
-                           __float_as_uint(acc.w));
-        } else {
-          float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-          for (int s = 0; s < kMaxWorld; ++s) {
-            if (s < p.world) {
-              const uint32_t w[4] = {raw[s][t].x, raw[s][t].y, raw[s][t].z, raw[s][t].w};
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const float2 f = unpack2(w[i], bf16);
-                acc[2 * i] += f.x;
-                acc[2 * i + 1] += f.y;
-              }
-            }
-          }
-          res = make_uint4(pack2(acc[0], acc[1], bf16), pack2(acc[2], acc[3], bf16),
-                           pack2(acc[4], acc[5], bf16), pack2(acc[6], acc[7], bf16));
-        }
-        const size_t o = static_cast<size_t>(row0 + (it0 + t) * 4 + r_in) * pitch + colb;
-        st_global_v4(out + o, res);
-      }
-    }
+      rs_sum_unit<kMaxWorld, 2>(p, parity, slot_bytes, pitch, row0, r_in, colb, out, bf16);
     }
     __syncwarp();
   }
@@ -723,7 +735,8 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     // -------------------------------------------------------- comm warps (every CTA)
     if (cta == 0 && aux == 1 && lane < p.world && lane != p.rank)
       st_release_sys(p.sig_peer[lane] + kSigReady + p.rank, p.epoch);   // my previous launch is over
-    const int na = kSplit ? 2 : n_aux;                       // warps 8.. split operands in 3xTF32
+    int na = kSplit ? 2 : n_aux;                             // warps 8.. split operands in 3xTF32
+    if (p.comm_warps > 0 && p.comm_warps < na) na = p.comm_warps;
     if (aux < na) {
       Tracer<kTrace> tr(p, (warp == 2 && lane == 0) ? cta : -1, 3);
       tr.ev(kEvStart, 0);

@@ -41,6 +41,7 @@ class TpGemmConfig(Structure):
         ("rank", c_int32), ("world", c_int32), ("chunk_rows", c_int32),
         ("ag_transport", c_int32), ("epi_transport", c_int32), ("rs_transport", c_int32),
         ("unrotated", c_int32), ("fp32_mode", c_int32), ("epilogue_act", c_int32),
+        ("comm_warps", c_int32), ("reserved", c_int32),
         ("m", c_int64), ("n", c_int64), ("k", c_int64),
         ("a", c_void_p), ("b", c_void_p),
         ("out", c_void_p * MAX_WORLD), ("peer_a", c_void_p * MAX_WORLD),
@@ -112,6 +113,7 @@ def lib() -> ctypes.CDLL:
     L.ddlb_vmm_has_multicast.argtypes = [c_void_p]
     L.ddlb_barrier_raw.argtypes = [POINTER(c_void_p), c_int, c_int, c_uint32, c_void_p]
     L.ddlb_copy.argtypes = [c_void_p, c_void_p, c_int64, c_int, c_void_p]
+    L.ddlb_max_active_clusters.argtypes = [c_int, c_int, POINTER(c_int)]
     L.ddlb_read_error_word.argtypes = [POINTER(c_uint32 * 4)]
     _lib = L
     return L

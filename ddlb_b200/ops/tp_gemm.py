@@ -191,7 +191,7 @@ class FusedAllGatherGemm(_FusedBase):
                  cta_group: int = 0, block_n: int = 0, group_m: int = 0, num_sms: int = 0,
                  b_is_nk: bool = False, transport: str = "auto", trace: bool = False,
                  fp32_mode: str = "3xtf32", unrotated: bool = False,
-                 activation: Optional[str] = None, out=None):
+                 activation: Optional[str] = None, out=None, comm_warps: int = 0):
         super().__init__(heap, rank, world)
         import torch
         if m % world:
@@ -210,6 +210,7 @@ class FusedAllGatherGemm(_FusedBase):
                                rank, world, layout, cta_group, block_n, group_m, num_sms,
                                chunk_rows, **common)
             cfg.ag_transport = AG_TRANSPORTS[self.transport]
+            cfg.comm_warps = int(comm_warps)
             if world == 1:
                 # nothing to gather: an ordinary device buffer, no symmetric heap needed
                 self.a_gathered = torch.empty(m, k, dtype=dtype, device=b.device)

@@ -52,7 +52,25 @@ def topology_report(comm=None) -> Dict[str, Any]:
     report["all_peers_accessible"] = bool(devs) and all(
         all(p["access"] == 1 for p in d["peers"]) for d in devs)
     report["multicast_supported"] = bool(devs) and all(d["multicast_supported"] == 1 for d in devs)
+    report["max_active_clusters"] = max_active_clusters()
     return report
+
+
+def max_active_clusters() -> Dict[str, int]:
+    """Resident clusters of the flagship GEMM kernel per cluster size on the current device
+    (clusters are confined to a GPC, so 148 SMs need not give 148 / size of them)."""
+    import ctypes
+    from .. import _native as N
+    out = {}
+    try:
+        lib = N.lib()
+        for size in (1, 2, 4, 8):
+            n = ctypes.c_int(0)
+            if lib.ddlb_max_active_clusters(size, 256, ctypes.byref(n)) == 0:
+                out[str(size)] = int(n.value)
+    except Exception:
+        pass
+    return out
 
 
 if __name__ == "__main__":

@@ -18,6 +18,7 @@ valid heap (``has_multicast`` False, the ``multimem`` transports refuse it).
 """
 from __future__ import annotations
 
+import array
 import ctypes
 import os
 import socket
@@ -114,7 +115,10 @@ class VmmHeap(SymmetricHeap):
                 tx = socket.socket(socket.AF_UNIX, socket.SOCK_DGRAM)
                 for p in range(self.world):
                     if p != self.rank:
-                        socket.send_fds(tx, [bytes([self.rank])], [fd], address=self._sock_path(tag, p))
+                        # (socket.send_fds drops its `address` argument in CPython 3.12)
+                        tx.sendmsg([bytes([self.rank])],
+                                   [(socket.SOL_SOCKET, socket.SCM_RIGHTS, array.array("i", [fd]))],
+                                   0, self._sock_path(tag, p))
                 tx.close()
             expected = len([s for s in senders if s != self.rank])
             for _ in range(expected):

@@ -124,6 +124,8 @@ typedef struct ddlb_tp_gemm_config {
   int32_t fp32_mode;     /* DDLB_FP32_* */
   int32_t epilogue_act;  /* DDLB_ACT_*: applied to the fp32 accumulator before the output is
                           * rounded (PLAIN / AG_*; not on tp_rowwise partial sums) */
+  int32_t comm_warps;    /* AG_BEFORE: aux warps per CTA that move data, 0 = all (6) */
+  int32_t reserved;
   int64_t m, n, k;       /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
   /* PLAIN:     a = A[m,k]                 out[rank] = C[m,n]
    * AG_BEFORE: a = gathered A[m,k] (own shard rows already in place), peer_a[r] = rank r's
@@ -194,6 +196,10 @@ int ddlb_debug_tile_coords(const ddlb_tp_gemm_config* cfg, int32_t first, int32_
 /* units {src, chunk, begin, end, base} moved by the default AG_BEFORE transport of cfg->rank;
  * pass out = NULL to get the count */
 int ddlb_debug_pull_units(const ddlb_tp_gemm_config* cfg, int64_t cap, int64_t* out, int64_t* count);
+
+/* Diagnostic: how many clusters of `cluster_size` CTAs (flagship kernel, `threads` per CTA) fit
+ * on the current device at once (clusters are confined to a GPC). */
+int ddlb_max_active_clusters(int cluster_size, int threads, int* out);
 
 /* Diagnostic: copy `bytes` (multiple of 16) with a 128-bit load/store kernel on `blocks` CTAs
  * (0 = 4 per SM). With a peer-mapped src it measures pull bandwidth, with a peer-mapped dst push. */

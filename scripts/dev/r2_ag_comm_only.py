@@ -40,15 +40,17 @@ def main():
         print(f"world {d} heap {type(heap).__name__} multicast {mc}", flush=True)
     for n in (64, 1024):
         b = torch.randn(k, n, device=comm.device, dtype=dt)
-        cases = [("AG_before", t) for t in ["pull", "push"] + (["multimem"] if mc else [])]
-        cases += [("AG_after", t) for t in ["tma", "st128"] + (["multimem"] if mc else [])]
-        for order, transport in cases:
+        cases = [("AG_before", "pull", w) for w in (2, 4, 6)]
+        cases += [("AG_before", t, 0) for t in ["push"] + (["multimem"] if mc else [])]
+        cases += [("AG_after", t, 0) for t in ["tma", "st128"] + (["multimem"] if mc else [])]
+        for order, transport, warps in cases:
             moved = (d - 1) / d * m * (k if order == "AG_before" else n) * 2
-            op = FusedAllGatherGemm(heap, r, d, m, n, k, dt, b, order=order, transport=transport)
+            op = FusedAllGatherGemm(heap, r, d, m, n, k, dt, b, order=order, transport=transport,
+                                    comm_warps=warps)
             op.a_shard.normal_()
             med, best = timed(comm, heap, op)
             if r == 0:
-                print(f"n={n:5d} {order:9s} transport={transport:8s} median {med * 1e3:7.1f} us (best "
+                print(f"n={n:5d} {order:9s} transport={transport:8s} warps={warps} median {med * 1e3:7.1f} us (best "
                       f"{best * 1e3:7.1f})  inbound {moved / (med * 1e6):6.1f} GB/s  info={op.plan.info}",
                       flush=True)
             op.close()
