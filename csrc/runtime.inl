@@ -227,6 +227,128 @@ extern "C" int ddlb_copy(void* dst, const void* src, int64_t bytes, int blocks, 
   return 0;
 }
 
+// Access-pattern diagnostic for the in-kernel collectives: the same bytes copied with the
+// patterns the fused kernels can use, on a chosen grid x block.
+//   pattern 0: dense grid-stride, 16 B per thread, 8 loads in flight (the copy_kernel above)
+//   pattern 1: every warp streams its own `unit_bytes` units (round-robin), two 4 KiB register
+//              groups in flight (copy_pipelined) - the round-2 comm warps
+//   pattern 2: warps interleave at 4 KiB: warp w moves pieces w, w + nw, ... so the whole grid
+//              sweeps the buffer densely; two pieces in flight per warp
+//   pattern 3: like 2 with 16 KiB in flight per warp (four pieces)
+namespace ddlb {
+// flags: bit 0 loads bypass L1 (ld.global.cg instead of .cs); bit 1 pattern 1 fences and bumps a
+// counter after every unit like the comm warps do; bit 2 (with bit 1) the first group of the
+// NEXT unit is already in flight when the fence is issued.
+template <bool kCg>
+__device__ __forceinline__ uint4 ld_peer(const uint8_t* p) {
+  return kCg ? __ldcg(reinterpret_cast<const uint4*>(p)) : __ldcs(reinterpret_cast<const uint4*>(p));
+}
+
+template <bool kCg>
+__device__ __forceinline__ void copy_units(uint8_t* dst, const uint8_t* src, size_t bytes, uint32_t unit_bytes,
+                                           int flags, uint32_t* counter, size_t gw, size_t nw, int lane) {
+  const size_t units = bytes / unit_bytes;
+  const uint32_t l16 = static_cast<uint32_t>(lane) * 16u;
+  const bool fence = (flags & 2) != 0, prefetch = (flags & 4) != 0;
+  uint4 va[kCopyGroup], vb[kCopyGroup];
+  bool have_a = false;
+  for (size_t u = gw; u < units; u += nw) {
+    const uint8_t* s0 = src + u * unit_bytes;
+    uint8_t* d0 = dst + u * unit_bytes;
+    if (!have_a) {
+#pragma unroll
+      for (int i = 0; i < kCopyGroup; ++i) va[i] = ld_peer<kCg>(s0 + l16 + i * 512);
+    }
+    have_a = false;
+    for (uint32_t off = 0; off < unit_bytes; off += 2 * kCopyStep) {
+#pragma unroll
+      for (int i = 0; i < kCopyGroup; ++i) vb[i] = ld_peer<kCg>(s0 + off + kCopyStep + l16 + i * 512);
+#pragma unroll
+      for (int i = 0; i < kCopyGroup; ++i) __stcg(reinterpret_cast<uint4*>(d0 + off + l16 + i * 512), va[i]);
+      if (off + 2 * kCopyStep < unit_bytes) {
+#pragma unroll
+        for (int i = 0; i < kCopyGroup; ++i) va[i] = ld_peer<kCg>(s0 + off + 2 * kCopyStep + l16 + i * 512);
+      } else if (prefetch && u + nw < units) {
+        const uint8_t* s1 = src + (u + nw) * unit_bytes;
+#pragma unroll
+        for (int i = 0; i < kCopyGroup; ++i) va[i] = ld_peer<kCg>(s1 + l16 + i * 512);
+        have_a = true;
+      }
+#pragma unroll
+      for (int i = 0; i < kCopyGroup; ++i)
+        __stcg(reinterpret_cast<uint4*>(d0 + off + kCopyStep + l16 + i * 512), vb[i]);
+    }
+    if (fence) {
+      __threadfence();
+      __syncwarp();
+      if (lane == 0) red_add_release_gpu(counter + (u & 63), 1u);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(512) copy_pattern_kernel(uint8_t* __restrict__ dst,
+                                                           const uint8_t* __restrict__ src, size_t bytes,
+                                                           int pattern, uint32_t unit_bytes, int flags,
+                                                           uint32_t* counter) {
+  extern __shared__ uint8_t carve_out[];      // only to shrink the L1 like the GEMM's operand ring does
+  if (threadIdx.x == 0 && bytes == 1) carve_out[0] = 0;
+  const int lane = threadIdx.x & 31;
+  const size_t gw = (static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const size_t nw = (static_cast<size_t>(gridDim.x) * blockDim.x) >> 5;
+  if (pattern == 1) {
+    if (flags & 1) copy_units<true>(dst, src, bytes, unit_bytes, flags, counter, gw, nw, lane);
+    else copy_units<false>(dst, src, bytes, unit_bytes, flags, counter, gw, nw, lane);
+    return;
+  }
+  const size_t pieces = bytes / kCopyStep;
+  const int depth = pattern == 3 ? 4 : 2;
+  // `depth` pieces in flight: load all, then store all
+  for (size_t p0 = gw; p0 < pieces; p0 += nw * depth) {
+    uint4 v[4][kCopyGroup];
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+      const size_t pc = p0 + static_cast<size_t>(d) * nw;
+      if (d < depth && pc < pieces) {
+#pragma unroll
+        for (int i = 0; i < kCopyGroup; ++i)
+          v[d][i] = __ldcs(reinterpret_cast<const uint4*>(src + pc * kCopyStep + lane * 16 + i * 512));
+      }
+    }
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+      const size_t pc = p0 + static_cast<size_t>(d) * nw;
+      if (d < depth && pc < pieces) {
+#pragma unroll
+        for (int i = 0; i < kCopyGroup; ++i)
+          __stcg(reinterpret_cast<uint4*>(dst + pc * kCopyStep + lane * 16 + i * 512), v[d][i]);
+      }
+    }
+  }
+}
+__device__ uint32_t g_copy_pattern_counter[64];
+}  // namespace ddlb
+
+extern "C" int ddlb_copy_pattern(void* dst, const void* src, int64_t bytes, int blocks, int threads,
+                                 int pattern, int unit_bytes, int smem_bytes, int flags, void* stream) {
+  using namespace ddlb;
+  if (bytes % (32 * 1024) != 0 || unit_bytes <= 0 || unit_bytes % 8192 != 0 || bytes % unit_bytes != 0)
+    return set_error("bytes must be a multiple of 32 KiB and of unit_bytes (a multiple of 8192)");
+  if (threads <= 0 || threads > 512 || threads % 32 != 0 || blocks <= 0) return set_error("bad launch shape");
+  if (pattern == 0) {
+    copy_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<uint4*>(dst), static_cast<const uint4*>(src), static_cast<size_t>(bytes / 16));
+  } else {
+    uint32_t* counter = nullptr;
+    DDLB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&counter), g_copy_pattern_counter));
+    DDLB_CUDA(cudaFuncSetAttribute(copy_pattern_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    copy_pattern_kernel<<<blocks, threads, static_cast<size_t>(smem_bytes), static_cast<cudaStream_t>(stream)>>>(
+        static_cast<uint8_t*>(dst), static_cast<const uint8_t*>(src), static_cast<size_t>(bytes), pattern,
+        static_cast<uint32_t>(unit_bytes), flags, counter);
+  }
+  DDLB_CUDA(cudaGetLastError());
+  return 0;
+}
+
 // Barrier on caller-provided signal pads (one pad base per rank, as seen from this process):
 // the same kernel as ddlb_symm_barrier for heaps that are not ddlb_symm objects (VMM heap).
 extern "C" int ddlb_barrier_raw(void* const* pad_bases, int rank, int world, uint32_t epoch, void* stream) {

@@ -198,6 +198,38 @@ __device__ __forceinline__ float2 unpack2(uint32_t w, bool bf16) {
 }
 
 // ---------------------------------------------------------------------------
+// Opt-in device trace: a timeline of one launch without a profiler (ncu cannot replay
+// kernels that wait for other ranks). Compiled in only for kTrace instantiations, so the
+// production kernels carry no trace code at all.
+// ---------------------------------------------------------------------------
+constexpr int kTraceSlots = 128;
+constexpr int kTraceRoles = 4;   // 0 producer, 1 mma, 2 epilogue (warp 4), 3 aux (warp 2)
+enum : uint32_t {
+  kEvStart = 1, kEvTileBegin = 2, kEvFlagWaited = 3, kEvTileIssued = 4, kEvAccReady = 5,
+  kEvUnitReady = 6, kEvTileStored = 7, kEvUnitDone = 8, kEvEnd = 9,
+};
+
+template <bool kTrace>
+struct Tracer {
+  uint4* base;
+  int n;
+  __device__ __forceinline__ Tracer(const TpGemmParams& p, int cta, int role) : base(nullptr), n(0) {
+    if constexpr (kTrace) {
+      if (p.trace != nullptr && cta >= 0)
+        base = p.trace + (static_cast<size_t>(cta) * kTraceRoles + role) * kTraceSlots;
+    }
+  }
+  __device__ __forceinline__ void ev(uint32_t tag, uint32_t arg) {
+    if constexpr (kTrace) {
+      if (base != nullptr && n < kTraceSlots) {
+        const uint64_t t = globaltimer_ns();
+        base[n++] = make_uint4(tag, arg, static_cast<uint32_t>(t), static_cast<uint32_t>(t >> 32));
+      }
+    }
+  }
+};
+
+// ---------------------------------------------------------------------------
 // AG_BEFORE: aux warps of EVERY CTA move the A shards (register path).
 // Measured on B200/NVSwitch: a 128-bit load/store copy reaches ~700 GB/s to or from a peer
 // while cp.async.bulk through shared memory stays near 400 GB/s, and a handful of dedicated
@@ -272,26 +304,77 @@ __device__ __forceinline__ void copy_pipelined(uint8_t* dst, const uint8_t* src,
 }
 
 // PULL (default): every unit of every peer's shard is read from the peer's buffer into
-// registers and stored locally, then the local chunk counter is bumped. At the end each warp
+// registers and stored locally, then the local chunk counter is bumped. Units are CLAIMED from
+// a queue head in fetch order (a static deal left the slowest warp 20 us behind the fastest
+// after seven units, and the GEMM waits for the last chunk), and the first 4 KiB of the next
+// unit are already in flight when the fence of the current one is issued, so a warp always has
+// 4..8 KiB outstanding. Measured on B200 (device trace, 2 ranks): 2 warps per CTA move a unit in
+// ~12.7 us = ~590 GB/s in total, the rate of a plain copy kernel with both directions busy; 6
+// warps per CTA oversubscribe the fabric (28 us per unit, lower total). At the end each warp
 // tells every peer that it will not read that peer's shard again in this launch.
-__device__ __forceinline__ void comm_warp_pull(const TpGemmParams& p, int gw, int nw, int lane) {
+template <bool kTrace>
+__device__ __forceinline__ void comm_warp_pull(const TpGemmParams& p, int lane, Tracer<kTrace>& tr) {
   const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
   const int upc = static_cast<int>((p.chunk_bytes + kPushUnit - 1) / kPushUnit);
   const int total = chunks_per_part * (p.world - 1) * upc;
   const size_t part_bytes = static_cast<size_t>(p.chunk_bytes) * chunks_per_part;
+  uint32_t* head = p.sig_local + kSigClaim + (p.epoch & 1u);
+  const uint32_t l16 = static_cast<uint32_t>(lane) * 16u;
 
   // a peer's shard is final once that peer has started this launch
   if (lane < p.world && lane != p.rank) wait_flag_ge<true>(p.sig_local + kSigReady + lane, p.epoch);
   __syncwarp();
+  tr.ev(kEvFlagWaited, 0);
 
-  for (int u = gw; u < total; u += nw) {
-    const CommUnit cu = pull_unit(p, u, upc, part_bytes);
-    copy_pipelined(p.local_a + cu.base, p.peer_a[cu.src] + cu.base, cu.begin, cu.end, lane);
+  auto claim = [&]() {
+    int u = 0;
+    if (lane == 0) u = static_cast<int>(atomicAdd(head, 1u));
+    return __shfl_sync(0xffffffffu, u, 0);
+  };
+#define DDLB_LD_GROUP(v, from, off, lim)                                               \
+  _Pragma("unroll") for (int i = 0; i < kCopyGroup; ++i) {                             \
+    const uint32_t o = (off) + l16 + static_cast<uint32_t>(i) * 512u;                  \
+    if (o < (lim)) v[i] = __ldcs(reinterpret_cast<const uint4*>((from) + o));          \
+  }
+#define DDLB_ST_GROUP(v, to, off, lim)                                                 \
+  _Pragma("unroll") for (int i = 0; i < kCopyGroup; ++i) {                             \
+    const uint32_t o = (off) + l16 + static_cast<uint32_t>(i) * 512u;                  \
+    if (o < (lim)) __stcg(reinterpret_cast<uint4*>((to) + o), v[i]);                   \
+  }
+  uint4 va[kCopyGroup], vb[kCopyGroup];
+  int u = claim();
+  CommUnit cu = pull_unit(p, u < total ? u : 0, upc, part_bytes);
+  if (u < total) {
+    const uint8_t* s0 = p.peer_a[cu.src] + cu.base;
+    DDLB_LD_GROUP(va, s0, cu.begin, cu.end)
+  }
+  while (u < total) {
+    const uint8_t* s0 = p.peer_a[cu.src] + cu.base;
+    uint8_t* d0 = p.local_a + cu.base;
+    const int un = claim();
+    const CommUnit cn = pull_unit(p, un < total ? un : 0, upc, part_bytes);
+    for (uint32_t off = cu.begin; off < cu.end; off += 2 * kCopyStep) {
+      DDLB_LD_GROUP(vb, s0, off + kCopyStep, cu.end)
+      DDLB_ST_GROUP(va, d0, off, cu.end)
+      if (off + 2 * kCopyStep < cu.end) {
+        DDLB_LD_GROUP(va, s0, off + 2 * kCopyStep, cu.end)
+      } else if (un < total) {
+        const uint8_t* s1 = p.peer_a[cn.src] + cn.base;     // next unit: first group in flight
+        DDLB_LD_GROUP(va, s1, cn.begin, cn.end)
+      }
+      DDLB_ST_GROUP(vb, d0, off + kCopyStep, cu.end)
+    }
+    tr.ev(kEvUnitReady, static_cast<uint32_t>(u));      // stores issued
     __threadfence();
     __syncwarp();
     if (lane == 0)
       red_add_release_gpu(p.sig_local + kSigChunk + cu.src * chunks_per_part + cu.chunk, 1u);
+    tr.ev(kEvUnitDone, static_cast<uint32_t>(u));       // fenced and announced
+    u = un;
+    cu = cn;
   }
+#undef DDLB_LD_GROUP
+#undef DDLB_ST_GROUP
   __syncwarp();
   if (lane < p.world && lane != p.rank)
     red_add_release_sys(p.sig_peer[lane] + kSigDone + p.rank, 1u);
@@ -353,38 +436,6 @@ __device__ __forceinline__ void comm_warp_push(const TpGemmParams& p, int gw, in
   }
 }
 
-// ---------------------------------------------------------------------------
-// Opt-in device trace: a timeline of one launch without a profiler (ncu cannot replay
-// kernels that wait for other ranks). Compiled in only for kTrace instantiations, so the
-// production kernels carry no trace code at all.
-// ---------------------------------------------------------------------------
-constexpr int kTraceSlots = 128;
-constexpr int kTraceRoles = 4;   // 0 producer, 1 mma, 2 epilogue (warp 4), 3 aux (warp 2)
-enum : uint32_t {
-  kEvStart = 1, kEvTileBegin = 2, kEvFlagWaited = 3, kEvTileIssued = 4, kEvAccReady = 5,
-  kEvUnitReady = 6, kEvTileStored = 7, kEvUnitDone = 8, kEvEnd = 9,
-};
-
-template <bool kTrace>
-struct Tracer {
-  uint4* base;
-  int n;
-  __device__ __forceinline__ Tracer(const TpGemmParams& p, int cta, int role) : base(nullptr), n(0) {
-    if constexpr (kTrace) {
-      if (p.trace != nullptr && cta >= 0)
-        base = p.trace + (static_cast<size_t>(cta) * kTraceRoles + role) * kTraceSlots;
-    }
-  }
-  __device__ __forceinline__ void ev(uint32_t tag, uint32_t arg) {
-    if constexpr (kTrace) {
-      if (base != nullptr && n < kTraceSlots) {
-        const uint64_t t = globaltimer_ns();
-        base[n++] = make_uint4(tag, arg, static_cast<uint32_t>(t), static_cast<uint32_t>(t >> 32));
-      }
-    }
-  }
-};
-
 // Store one staged epilogue chunk (32 rows x 128 bytes, 128-byte swizzled in shared memory)
 // with 128-bit stores: per instruction the warp writes 4 rows x 128 contiguous bytes. Plain
 // stores move ~690 GB/s to a peer over NVLink; TMA stores were measured at ~400-530 GB/s.
@@ -413,67 +464,67 @@ __device__ __forceinline__ void store_chunk_st128(uint8_t* dst_base, size_t pitc
 }
 
 // Sum the d staged copies of this lane's share of one unit (8 row groups x 16 bytes) and write
-// the result. kGroups row groups of all d sources are loaded before the first add (up to 16
-// independent 16-byte loads in flight per lane). ONE instantiation on purpose: several inlined
-// (or called) variants make ptxas spill kilobytes in a kernel at its 168-register cap.
+// the result. Sixteen independent 16-byte loads are in flight per lane whatever d is: the
+// loads are numbered i = t * d + s (row group t, source s), so a running sum that is flushed
+// whenever s wraps needs no register array indexed by a run-time value (one round at d = 2, two
+// at d = 4, four at d = 8). ONE instantiation on purpose: several inlined (or called) variants
+// make ptxas spill kilobytes in a kernel that sits at its 168-register cap.
 // push: the d partials sit in the local staging slots [parity][src];
 // pull: in slot [parity][rank] of every rank's staging (peer loads).
-template <int kSrc, int kGroups>
 __device__ __forceinline__ void rs_sum_unit(const TpGemmParams& p, uint32_t parity, size_t slot_bytes,
                                             size_t pitch, int row0, int r_in, int colb, uint8_t* out,
                                             bool bf16) {
   const bool pull = p.rs_transport == kRsPull;
+  const int d = p.world;
+  const int groups = 16 / d;                       // row groups per round (d <= 8 -> >= 2)
+  const int per_round = groups * d;
 #pragma unroll 1
-  for (int it0 = 0; it0 < 8; it0 += kGroups) {
-    uint4 raw[kSrc][kGroups];
+  for (int t0 = 0; t0 < 8; t0 += groups) {
+    uint4 raw[16];
 #pragma unroll
-    for (int s = 0; s < kSrc; ++s) {
-      if (s < p.world) {
+    for (int i = 0; i < 16; ++i) {
+      const int t = i / d, s = i - t * d;
+      if (i < per_round && t0 + t < 8) {
         const uint8_t* src = pull
-            ? p.stage_base[s] + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes
-            : p.stage_base[p.rank] + (static_cast<size_t>(parity) * p.world + s) * slot_bytes;
-#pragma unroll
-        for (int t = 0; t < kGroups; ++t) {
-          const size_t o = static_cast<size_t>(row0 + (it0 + t) * 4 + r_in) * pitch + colb;
-          raw[s][t] = __ldcg(reinterpret_cast<const uint4*>(src + o));
-        }
+            ? p.stage_base[s] + (static_cast<size_t>(parity) * d + p.rank) * slot_bytes
+            : p.stage_base[p.rank] + (static_cast<size_t>(parity) * d + s) * slot_bytes;
+        const size_t o = static_cast<size_t>(row0 + (t0 + t) * 4 + r_in) * pitch + colb;
+        raw[i] = __ldcg(reinterpret_cast<const uint4*>(src + o));
       }
     }
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int t = 0; t < kGroups; ++t) {
-      uint4 res;
-      if (p.elem == 4) {
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = 0; i < 16; ++i) {
+      const int t = i / d, s = i - t * d;
+      if (i < per_round && t0 + t < 8) {
+        if (p.elem == 4) {
+          acc[0] += __uint_as_float(raw[i].x);
+          acc[1] += __uint_as_float(raw[i].y);
+          acc[2] += __uint_as_float(raw[i].z);
+          acc[3] += __uint_as_float(raw[i].w);
+        } else {
+          const uint32_t w[4] = {raw[i].x, raw[i].y, raw[i].z, raw[i].w};
 #pragma unroll
-        for (int s = 0; s < kSrc; ++s) {
-          if (s < p.world) {
-            acc.x += __uint_as_float(raw[s][t].x);
-            acc.y += __uint_as_float(raw[s][t].y);
-            acc.z += __uint_as_float(raw[s][t].z);
-            acc.w += __uint_as_float(raw[s][t].w);
+          for (int j = 0; j < 4; ++j) {
+            const float2 f = unpack2(w[j], bf16);
+            acc[2 * j] += f.x;
+            acc[2 * j + 1] += f.y;
           }
         }
-        res = make_uint4(__float_as_uint(acc.x), __float_as_uint(acc.y), __float_as_uint(acc.z),
-                         __float_as_uint(acc.w));
-      } else {
-        float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (s == d - 1) {                           // last source of row group t: flush
+          uint4 res;
+          if (p.elem == 4)
+            res = make_uint4(__float_as_uint(acc[0]), __float_as_uint(acc[1]), __float_as_uint(acc[2]),
+                             __float_as_uint(acc[3]));
+          else
+            res = make_uint4(pack2(acc[0], acc[1], bf16), pack2(acc[2], acc[3], bf16),
+                             pack2(acc[4], acc[5], bf16), pack2(acc[6], acc[7], bf16));
+          const size_t o = static_cast<size_t>(row0 + (t0 + t) * 4 + r_in) * pitch + colb;
+          st_global_v4(out + o, res);
 #pragma unroll
-        for (int s = 0; s < kSrc; ++s) {
-          if (s < p.world) {
-            const uint32_t w[4] = {raw[s][t].x, raw[s][t].y, raw[s][t].z, raw[s][t].w};
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const float2 f = unpack2(w[i], bf16);
-              acc[2 * i] += f.x;
-              acc[2 * i + 1] += f.y;
-            }
-          }
+          for (int j = 0; j < 8; ++j) acc[j] = 0.f;
         }
-        res = make_uint4(pack2(acc[0], acc[1], bf16), pack2(acc[2], acc[3], bf16),
-                         pack2(acc[4], acc[5], bf16), pack2(acc[6], acc[7], bf16));
       }
-      const size_t o = static_cast<size_t>(row0 + (it0 + t) * 4 + r_in) * pitch + colb;
-      st_global_v4(out + o, res);
     }
   }
 }
@@ -485,7 +536,9 @@ __device__ __forceinline__ void rs_sum_unit(const TpGemmParams& p, uint32_t pari
 // claim units from a queue head in the signal block (one head per epoch parity; the other
 // one is reset for the next launch).
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, bool bf16) {
+template <bool kTrace>
+__device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, bool bf16,
+                                               Tracer<kTrace>& tr) {
   const uint32_t parity = p.epoch & 1u;
   const int segs = p.block_n * p.elem / 128;            // 128-byte column segments per n-block
   const int units_per_tile = 4 * segs;
@@ -510,6 +563,7 @@ __device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, 
     const int colb = (nb * p.block_n) * p.elem + c * 128 + j * 16;
     if (lane == 0) wait_flag_ge<true>(p.sig_local + kSigChunk + tile, target);
     __syncwarp();
+    tr.ev(kEvUnitReady, static_cast<uint32_t>(u));
     const bool active = colb < static_cast<int>(pitch);   // n-blocks may overhang N
 
     if (!active) {
@@ -531,9 +585,10 @@ __device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, 
         st_global_v4(out + o, v[it]);
       }
     } else {
-      rs_sum_unit<kMaxWorld, 2>(p, parity, slot_bytes, pitch, row0, r_in, colb, out, bf16);
+      rs_sum_unit(p, parity, slot_bytes, pitch, row0, r_in, colb, out, bf16);
     }
     __syncwarp();
+    tr.ev(kEvUnitDone, static_cast<uint32_t>(u));
   }
 }
 
@@ -735,13 +790,17 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     // -------------------------------------------------------- comm warps (every CTA)
     if (cta == 0 && aux == 1 && lane < p.world && lane != p.rank)
       st_release_sys(p.sig_peer[lane] + kSigReady + p.rank, p.epoch);   // my previous launch is over
-    int na = kSplit ? 2 : n_aux;                             // warps 8.. split operands in 3xTF32
-    if (p.comm_warps > 0 && p.comm_warps < na) na = p.comm_warps;
+    // pull: 2 warps per CTA fill the links, more oversubscribe them (see comm_warp_pull);
+    // warps 8.. split operands in 3xTF32
+    int na = (kSplit || p.ag_transport == kAgPull) ? 2 : n_aux;
+    if (p.comm_warps > 0) na = p.comm_warps < n_aux ? p.comm_warps : n_aux;
+    if (kSplit && na > 2) na = 2;
+    if (cta == 0 && aux == 0 && lane == 0) p.sig_local[kSigClaim + ((p.epoch & 1u) ^ 1u)] = 0u;
     if (aux < na) {
       Tracer<kTrace> tr(p, (warp == 2 && lane == 0) ? cta : -1, 3);
       tr.ev(kEvStart, 0);
       const int gw = cta * na + aux, nw = nctas * na;
-      if (p.ag_transport == kAgPull) comm_warp_pull(p, gw, nw, lane);
+      if (p.ag_transport == kAgPull) comm_warp_pull<kTrace>(p, lane, tr);
       else if (p.ag_transport == kAgPushMulticast) comm_warp_push<true>(p, gw, nw, lane);
       else comm_warp_push<false>(p, gw, nw, lane);
       tr.ev(kEvEnd, 0);
@@ -755,7 +814,10 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
   } else if (aux >= 0 && p.mode == kModeRS && !(kSplit && warp >= 8)) {
     // -------------------------------------------------------- reducers (every CTA)
     if (cta == 0 && aux == 0 && lane == 0) p.sig_local[kSigClaim + ((p.epoch & 1u) ^ 1u)] = 0u;
-    rs_reduce_loop(p, lane, bf16);
+    Tracer<kTrace> tr(p, (warp == 2 && lane == 0) ? cta : -1, 3);
+    tr.ev(kEvStart, 0);
+    rs_reduce_loop<kTrace>(p, lane, bf16, tr);
+    tr.ev(kEvEnd, 0);
   } else if (warp >= 4 && warp < 8) {
     // -------------------------------------------------------- epilogue
     const int q = warp & 3;                                 // TMEM lane quadrant
@@ -898,7 +960,10 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
       }
     }
     // RS: help the aux warps with whatever is left of the reduction
-    if (p.mode == kModeRS) rs_reduce_loop(p, lane, bf16);
+    if (p.mode == kModeRS) {
+      Tracer<false> none(p, -1, 3);
+      rs_reduce_loop<false>(p, lane, bf16, none);
+    }
   }
 
   // ---------------------------------------------------------------- teardown

@@ -113,6 +113,7 @@ def lib() -> ctypes.CDLL:
     L.ddlb_vmm_has_multicast.argtypes = [c_void_p]
     L.ddlb_barrier_raw.argtypes = [POINTER(c_void_p), c_int, c_int, c_uint32, c_void_p]
     L.ddlb_copy.argtypes = [c_void_p, c_void_p, c_int64, c_int, c_void_p]
+    L.ddlb_copy_pattern.argtypes = [c_void_p, c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p]
     L.ddlb_max_active_clusters.argtypes = [c_int, c_int, POINTER(c_int)]
     L.ddlb_read_error_word.argtypes = [POINTER(c_uint32 * 4)]
     _lib = L

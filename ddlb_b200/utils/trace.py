@@ -17,7 +17,7 @@ from .. import _native as N
 
 ROLES = {0: "producer", 1: "mma", 2: "epilogue", 3: "comm"}
 TAGS = {1: "start", 2: "tile_begin", 3: "flag_waited", 4: "tile_issued", 5: "acc_ready",
-        6: "own_waited", 7: "tile_stored", 8: "comm_unit", 9: "end"}
+        6: "unit_ready", 7: "tile_stored", 8: "unit_done", 9: "end"}
 
 
 def alloc_trace_buffer(device, max_ctas: int = 160):

@@ -205,6 +205,14 @@ int ddlb_max_active_clusters(int cluster_size, int threads, int* out);
  * (0 = 4 per SM). With a peer-mapped src it measures pull bandwidth, with a peer-mapped dst push. */
 int ddlb_copy(void* dst, const void* src, int64_t bytes, int blocks, void* stream);
 
+/* Diagnostic: the same copy with the access patterns the fused kernels can use (0 dense
+ * grid-stride, 1 per-warp units of unit_bytes, 2/3 warps interleaved at 4 KiB with 8/16 KiB in
+ * flight per warp) on blocks x threads. See csrc/runtime.inl.
+ * smem_bytes of dynamic shared memory are requested only to shrink the L1 like the GEMM does;
+ * flags: 1 = loads bypass L1, 2 = fence + counter bump per unit, 4 = next unit prefetched. */
+int ddlb_copy_pattern(void* dst, const void* src, int64_t bytes, int blocks, int threads,
+                      int pattern, int unit_bytes, int smem_bytes, int flags, void* stream);
+
 /* device-side error word set by a kernel that timed out waiting ({code, block, aux0, aux1}) */
 int ddlb_read_error_word(uint32_t out[4]);
 
