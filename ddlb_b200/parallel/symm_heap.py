@@ -100,6 +100,32 @@ class SymmetricHeap:
         self._sig_cursor = off + 4 * words
         return off
 
+    def mark(self) -> Tuple[int, int]:
+        """Current allocation state, for ``release``."""
+        return self._cursor, self._sig_cursor
+
+    def release(self, mark: Tuple[int, int]) -> None:
+        """Rewind the bump allocator to ``mark`` (collective: every rank, same point, after all
+        ops that used the released memory were closed). The released signal words are zeroed
+        again and a barrier separates the clearing from the next user."""
+        torch = self._torch
+        cursor, sig_cursor = mark
+        if cursor > self._cursor or sig_cursor > self._sig_cursor:
+            raise ValueError("release() takes a mark taken earlier on this heap")
+        torch.cuda.synchronize()
+        if self.world > 1:
+            self.barrier()                       # nobody still signals into the old words
+            torch.cuda.synchronize()
+        if sig_cursor < self._sig_cursor:
+            n = self._sig_cursor - sig_cursor
+            raw = _RawCudaBuffer(self.base() + sig_cursor, n, self)
+            torch.as_tensor(raw, device=f"cuda:{self.device_index}").zero_()
+        self._cursor, self._sig_cursor = cursor, sig_cursor
+        torch.cuda.synchronize()
+        if self.world > 1:
+            self.barrier()
+            torch.cuda.synchronize()
+
     def ptr(self, offset: int, rank: Optional[int] = None) -> int:
         return self.base(rank) + offset
 
