@@ -306,6 +306,19 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map
   }
 }
 
+// One TMA load whose box lands at the same shared-memory offset in every CTA of `cta_mask`
+// (cta_group::2 form: the mbarrier operand names the even CTA of the issuing CTA's MMA pair; the
+// transaction bytes of every destination CTA are credited to the barrier at the same offset in
+// the even CTA of THAT destination's pair).
+__device__ __forceinline__ void tma_load_2d_multicast(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                                      int c0, int c1, uint16_t cta_mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      ".multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst), "l"(map), "r"(bar), "r"(c0),
+      "r"(c1), "h"(cta_mask)
+      : "memory");
+}
+
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map),
                "r"(src), "r"(c0), "r"(c1)
@@ -414,7 +427,7 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
 // Arrive on an mbarrier once all previously issued tcgen05.mma of this thread retired.
 // cta_group::2 multicasts the arrival to the same barrier offset in both CTAs of the pair.
 template <int kCtaGroup>
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
+__device__ __forceinline__ void umma_commit(uint32_t bar, uint16_t cta_mask = 0x3) {
   if constexpr (kCtaGroup == 1)
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
                  : "memory");
@@ -422,7 +435,7 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile(
         "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
         " [%0], %1;" ::"r"(bar),
-        "h"(static_cast<uint16_t>(0x3))
+        "h"(cta_mask)
         : "memory");
 }
 

@@ -52,6 +52,7 @@ struct Resolved {
   int split;     // 1: 3xTF32 (fp32 only)
   int threads;   // 256, or 384 when the aux warps 8..11 have work (collectives, 3xTF32)
   int part0;     // first shard in visiting order
+  int pairs;     // MMA pairs per cluster: 2 = four-CTA clusters with the A tile multicast
 };
 
 static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
@@ -94,6 +95,18 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
   if (r.split && r.cta_group == 1 && r.block_n == 256)
     return set_error("3xTF32 with cta_group=1 needs block_n=128 (shared memory)");
 
+  // two MMA pairs per cluster (A multicast): 16-bit, cta_group 2, BLOCK_N 256, an even number
+  // of n-blocks. Explicit request only for now (cluster_pairs = 2); 0 and 1 mean one pair.
+  if (c.cluster_pairs < 0 || c.cluster_pairs > 2) return set_error("cluster_pairs must be 0, 1 or 2");
+  r.pairs = c.cluster_pairs == 2 ? 2 : 1;
+  if (r.pairs == 2) {
+    const int64_t nb = (c.n + r.block_n - 1) / r.block_n;
+    if (r.elem != 2 || r.cta_group != 2 || r.block_n != 256 || nb % 2 != 0)
+      return set_error("cluster_pairs=2 needs fp16/bf16, cta_group=2, block_n=256 and an even number "
+                       "of 256-column blocks (n = %lld)", (long long)c.n);
+  }
+  const int cluster_ctas = r.cta_group * r.pairs;
+
   int dev = 0, sms = 0;
   if (cudaGetDevice(&dev) != cudaSuccess ||
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
@@ -103,8 +116,8 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
     sms = c.num_sms;
   }
   r.grid = c.num_sms > 0 ? (c.num_sms < sms ? c.num_sms : sms) : sms;
-  r.grid -= r.grid % r.cta_group;
-  if (r.grid < r.cta_group) return set_error("no SMs to launch on");
+  r.grid -= r.grid % cluster_ctas;
+  if (r.grid < cluster_ctas) return set_error("no SMs to launch on");
 
   r.group_m = c.group_m > 0 ? c.group_m : 8;
 
@@ -163,12 +176,15 @@ struct ddlb_tp_gemm_plan {
 
 namespace ddlb {
 
-template <int G, int BN, bool NM, bool F32 = false, bool SPLIT = false>
+static void fill_launch(cudaLaunchConfig_t& lc, cudaLaunchAttribute* attr, unsigned grid, int threads,
+                        int smem_bytes, int cta_group, cudaStream_t st);
+
+template <int G, int BN, bool NM, bool F32 = false, bool SPLIT = false, int PAIRS = 1>
 static int bind_kernel(ddlb_tp_gemm_plan* plan) {
   using Cfg = TpGemmCfg<G, BN, SPLIT>;
-  auto k = tp_gemm_kernel<G, BN, NM, F32, SPLIT>;
+  auto k = tp_gemm_kernel<G, BN, NM, F32, SPLIT, false, PAIRS>;
   plan->kernel = reinterpret_cast<void (*)(TpGemmParams)>(k);
-  auto ke = tp_gemm_emulated_kernel<G, BN, NM, F32, SPLIT>;
+  auto ke = tp_gemm_emulated_kernel<G, BN, NM, F32, SPLIT, PAIRS>;
   plan->emu_kernel = ke;
   plan->stages = Cfg::kStages;
   plan->smem_bytes = Cfg::kSmemBytes;
@@ -182,6 +198,20 @@ static int bind_kernel(ddlb_tp_gemm_plan* plan) {
   if (G == 2) {
     e = cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     if (e != cudaSuccess) (void)cudaGetLastError();
+  }
+  if (PAIRS == 2) {
+    // clusters are confined to a GPC: launch as many four-CTA clusters as can be resident
+    cudaLaunchConfig_t lc;
+    cudaLaunchAttribute attr[1];
+    fill_launch(lc, attr, static_cast<unsigned>(plan->res.grid), plan->res.threads, Cfg::kSmemBytes,
+                G * PAIRS, nullptr);
+    int fit = 0;
+    e = cudaOccupancyMaxActiveClusters(&fit, reinterpret_cast<const void*>(k), &lc);
+    if (e != cudaSuccess || fit < 1) {
+      (void)cudaGetLastError();
+      return set_error("cudaOccupancyMaxActiveClusters(cluster of 4): %s", cudaGetErrorString(e));
+    }
+    if (fit * G * PAIRS < plan->res.grid) plan->res.grid = fit * G * PAIRS;
   }
   return 0;
 }
@@ -219,6 +249,8 @@ static int select_kernel(ddlb_tp_gemm_plan* plan) {
     if (g == 2 && bn == 128) return bind_kernel<2, 128, false, true>(plan);
     return set_error("no fp32 kernel for cta_group=%d block_n=%d", g, bn);
   }
+  if (plan->res.pairs == 2)
+    return nm ? bind_kernel<2, 256, true, false, false, 2>(plan) : bind_kernel<2, 256, false, false, false, 2>(plan);
   if (g == 1 && bn == 256) return nm ? bind_kernel<1, 256, true>(plan) : bind_kernel<1, 256, false>(plan);
   if (g == 2 && bn == 256) return nm ? bind_kernel<2, 256, true>(plan) : bind_kernel<2, 256, false>(plan);
   if (g == 1 && bn == 128) return nm ? bind_kernel<1, 128, true>(plan) : bind_kernel<1, 128, false>(plan);
@@ -237,6 +269,7 @@ static void fill_schedule(TpGemmParams& p, const ddlb_tp_gemm_config& c, const R
   p.world = c.world;
   p.num_m_blocks = (r.a_rows + r.tile_m - 1) / r.tile_m;
   p.num_n_blocks = static_cast<int>((c.n + r.block_n - 1) / r.block_n);
+  p.sched_n_blocks = p.num_n_blocks / r.pairs;
   p.group_m = r.group_m;
   p.part_rows = r.part_rows;
   p.out_n = static_cast<int>(c.n);
@@ -313,7 +346,8 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   {  // A: [a_rows, K] row-major, box = one 128-byte row segment x 128 rows
     const uint64_t dims[2] = {K, static_cast<uint64_t>(r.a_rows)};
     const uint64_t strides[1] = {K * E};
-    const uint32_t box[2] = {row_elems, kBlockM};
+    // two pairs per cluster: every CTA loads half of its 128 rows and multicasts them
+    const uint32_t box[2] = {row_elems, static_cast<uint32_t>(kBlockM / r.pairs)};
     rc = make_tmap(&p.tmA, c.a, 2, dims, strides, box, r.elem);
   }
   if (rc == 0) {
@@ -391,7 +425,7 @@ extern "C" int ddlb_tp_gemm_run(ddlb_tp_gemm_plan* plan, uint32_t epoch, void* s
   cudaLaunchConfig_t lc;
   cudaLaunchAttribute attr[1];
   fill_launch(lc, attr, static_cast<unsigned>(plan->res.grid), plan->res.threads, plan->smem_bytes,
-              plan->res.cta_group, static_cast<cudaStream_t>(stream));
+              plan->res.cta_group * plan->res.pairs, static_cast<cudaStream_t>(stream));
   void* args[1] = {&plan->params};
   cudaError_t e = cudaLaunchKernelExC(&lc, reinterpret_cast<const void*>(plan->kernel), args);
   if (e != cudaSuccess) {
@@ -430,16 +464,27 @@ extern "C" int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, u
     if (plans[r] == nullptr) return set_error("null plan %d", r);
     if (plans[r]->emu_kernel == nullptr) return set_error("traced plans cannot be emulated");
     if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group ||
-        plans[r]->res.threads != first->res.threads)
+        plans[r]->res.threads != first->res.threads || plans[r]->res.pairs != first->res.pairs)
       return set_error("emulated ranks must use the same kernel variant");
   }
   int dev = 0, sms = 0;
   DDLB_CUDA(cudaGetDevice(&dev));
   DDLB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int g = first->res.cta_group;
+  const int g = first->res.cta_group * first->res.pairs;   // CTAs per cluster
   int clusters_per_rank = (sms / world) / g;
   const int want = first->res.grid / g;            // honour a smaller num_sms request
   if (first->cfg.num_sms > 0 && want < clusters_per_rank) clusters_per_rank = want;
+  if (first->res.pairs == 2) {
+    // four-CTA clusters are confined to a GPC: fewer fit than sms / 4, and an emulated launch
+    // must be fully resident
+    cudaLaunchConfig_t probe;
+    cudaLaunchAttribute pattr[1];
+    fill_launch(probe, pattr, static_cast<unsigned>(sms - sms % g), first->res.threads, first->smem_bytes, g,
+                nullptr);
+    int fit = 0;
+    DDLB_CUDA(cudaOccupancyMaxActiveClusters(&fit, reinterpret_cast<const void*>(first->emu_kernel), &probe));
+    if (fit / world < clusters_per_rank) clusters_per_rank = fit / world;
+  }
   if (clusters_per_rank < 1) return set_error("no cluster left per emulated rank");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   TpGemmParams* dparams = nullptr;
@@ -522,16 +567,27 @@ extern "C" int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int w
     if (plans[r] == nullptr) return set_error("null plan %d", r);
     if (plans[r]->emu_kernel == nullptr) return set_error("traced plans cannot be emulated");
     if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group ||
-        plans[r]->res.threads != first->res.threads)
+        plans[r]->res.threads != first->res.threads || plans[r]->res.pairs != first->res.pairs)
       return set_error("emulated ranks must use the same kernel variant");
   }
   int dev = 0, sms = 0;
   DDLB_CUDA(cudaGetDevice(&dev));
   DDLB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int g = first->res.cta_group;
+  const int g = first->res.cta_group * first->res.pairs;   // CTAs per cluster
   int clusters_per_rank = (sms / world) / g;
   const int want = first->res.grid / g;
   if (first->cfg.num_sms > 0 && want < clusters_per_rank) clusters_per_rank = want;
+  if (first->res.pairs == 2) {
+    // four-CTA clusters are confined to a GPC: fewer fit than sms / 4, and an emulated launch
+    // must be fully resident
+    cudaLaunchConfig_t probe;
+    cudaLaunchAttribute pattr[1];
+    fill_launch(probe, pattr, static_cast<unsigned>(sms - sms % g), first->res.threads, first->smem_bytes, g,
+                nullptr);
+    int fit = 0;
+    DDLB_CUDA(cudaOccupancyMaxActiveClusters(&fit, reinterpret_cast<const void*>(first->emu_kernel), &probe));
+    if (fit / world < clusters_per_rank) clusters_per_rank = fit / world;
+  }
   if (clusters_per_rank < 1) return set_error("no cluster left per emulated rank");
 
   TpGemmParams* dparams = nullptr;
@@ -595,6 +651,7 @@ extern "C" int ddlb_debug_schedule(const ddlb_tp_gemm_config* cfg, int32_t out[1
   out[0] = p.num_m_blocks; out[1] = p.num_n_blocks; out[2] = p.mblks_per_part; out[3] = p.chunk_mblks;
   out[4] = p.group_m; out[5] = r.tile_m; out[6] = r.block_n; out[7] = r.cta_group;
   out[8] = r.chunk_rows; out[9] = r.part0; out[10] = r.grid; out[11] = r.threads;
+  (void)p.sched_n_blocks;
   return 0;
 }
 
@@ -607,7 +664,7 @@ extern "C" int ddlb_debug_tile_coords(const ddlb_tp_gemm_config* cfg, int32_t fi
   TpGemmParams p;
   memset(&p, 0, sizeof(p));
   fill_schedule(p, *cfg, r);
-  const int total = p.num_m_blocks * p.num_n_blocks;
+  const int total = p.num_m_blocks * p.sched_n_blocks;
   if (first + count > total) return set_error("tiles %d..%d out of range (%d tiles)", first, first + count, total);
   for (int i = 0; i < count; ++i) {
     const TileCoord tc = tile_coord(p, first + i);

@@ -72,6 +72,7 @@ struct TpGemmParams {
   int rank, world;
   int num_m_blocks;       // cluster tiles along M (of the A operand map)
   int num_n_blocks;
+  int sched_n_blocks;     // n-blocks the tile order sees: num_n_blocks / pairs (cluster of 2 MMA pairs)
   int num_k_blocks;
   int group_m;            // rasterisation: m-blocks per group (L2 reuse)
   int mblks_per_part;     // cluster tiles per rank shard (AG_BEFORE / RS), else num_m_blocks
@@ -137,7 +138,7 @@ struct TileCoord {
 // Linear tile index -> tile, identical in every role. Grouped rasterisation over an
 // arrival-ordered sequence of m-blocks.
 __host__ __device__ __forceinline__ TileCoord tile_coord(const TpGemmParams& p, int t) {
-  const int per_group = p.group_m * p.num_n_blocks;
+  const int per_group = p.group_m * p.sched_n_blocks;
   const int group = t / per_group;
   const int within = t - group * per_group;
   const int first = group * p.group_m;
@@ -472,8 +473,8 @@ __device__ __forceinline__ void store_chunk_st128(uint8_t* dst_base, size_t pitc
 // push: the d partials sit in the local staging slots [parity][src];
 // pull: in slot [parity][rank] of every rank's staging (peer loads).
 __device__ __forceinline__ void rs_sum_unit(const TpGemmParams& p, uint32_t parity, size_t slot_bytes,
-                                            size_t pitch, int row0, int r_in, int colb, uint8_t* out,
-                                            bool bf16) {
+                                            size_t unit_off, size_t pitch, int row0, int r_in, int colb,
+                                            uint8_t* out, bool bf16) {
   const bool pull = p.rs_transport == kRsPull;
   const int d = p.world;
   const int groups = 16 / d;                       // row groups per round (d <= 8 -> >= 2)
@@ -488,8 +489,7 @@ __device__ __forceinline__ void rs_sum_unit(const TpGemmParams& p, uint32_t pari
         const uint8_t* src = pull
             ? p.stage_base[s] + (static_cast<size_t>(parity) * d + p.rank) * slot_bytes
             : p.stage_base[p.rank] + (static_cast<size_t>(parity) * d + s) * slot_bytes;
-        const size_t o = static_cast<size_t>(row0 + (t0 + t) * 4 + r_in) * pitch + colb;
-        raw[i] = __ldcg(reinterpret_cast<const uint4*>(src + o));
+        raw[i] = __ldcg(reinterpret_cast<const uint4*>(src + unit_off + ((t0 + t) * 4 + r_in) * 128));
       }
     }
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -544,7 +544,10 @@ __device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, 
   const int units_per_tile = 4 * segs;
   const int total = p.rs_tiles * units_per_tile;
   const size_t pitch = static_cast<size_t>(p.out_n) * p.elem;
-  const size_t slot_bytes = static_cast<size_t>(p.part_rows) * pitch;
+  // staging is UNIT-major: unit u (32 rows x 128 bytes of one tile) is one contiguous 4 KiB block,
+  // so a partial tile crosses NVLink as 512 contiguous bytes per warp instruction instead of four
+  // 128-byte row segments 2 KiB apart; only the final output is row-major
+  const size_t slot_bytes = static_cast<size_t>(total) * kEpiBufBytes;
   const uint32_t target = 4u * static_cast<uint32_t>(p.world) * p.epoch;
   uint32_t* head = p.sig_local + kSigClaim + parity;
   const int r_in = lane >> 3, j = lane & 7;
@@ -570,11 +573,12 @@ __device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, 
       // nothing in this 16-byte column for this lane; stay converged for the next claim
     } else if (p.rs_transport == kRsPullMulticast) {
       // one load per 16 bytes returns the sum over all ranks, added in the NVSwitch
-      const uint8_t* src = p.mc_ptr + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes;
+      const uint8_t* src = p.mc_ptr + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes +
+                           static_cast<size_t>(u) * kEpiBufBytes + j * 16;
       uint4 v[8];
 #pragma unroll
       for (int it = 0; it < 8; ++it) {
-        const size_t o = static_cast<size_t>(row0 + it * 4 + r_in) * pitch + colb;
+        const size_t o = static_cast<size_t>(it * 4 + r_in) * 128;
         if (p.elem == 4) v[it] = multimem_ld_reduce_f32x4(src + o);
         else if (bf16) v[it] = multimem_ld_reduce_bf16x8(src + o);
         else v[it] = multimem_ld_reduce_f16x8(src + o);
@@ -585,7 +589,8 @@ __device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, 
         st_global_v4(out + o, v[it]);
       }
     } else {
-      rs_sum_unit(p, parity, slot_bytes, pitch, row0, r_in, colb, out, bf16);
+      rs_sum_unit(p, parity, slot_bytes, static_cast<size_t>(u) * kEpiBufBytes + j * 16, pitch, row0, r_in,
+                  colb, out, bf16);
     }
     __syncwarp();
     tr.ev(kEvUnitDone, static_cast<uint32_t>(u));
@@ -602,12 +607,18 @@ __device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, 
 // per k-step (hi*hi + hi*lo + lo*hi), which restores ~fp32 accuracy
 // (BASELINE.json north star; the reference's default dtype is float32,
 // ddlb/primitives/TPColumnwise/tp_columnwise.py:32).
+// kPairs = 2: a cluster of FOUR CTAs = two MMA pairs that compute two neighbouring n-blocks of the
+// same 256 rows; the A tile is loaded once from L2 and multicast to both pairs. Measured (ncu):
+// with one pair per cluster the operand stream from L2 runs at the fabric's cap (~6.6 KB/clk,
+// 1.07 GB per 100 us launch) and the tensor pipe idles 22 % of its active cycles.
 template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kSplit = false,
-          bool kTrace = false>
+          bool kTrace = false, int kPairs = 1>
 __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cluster,
                                              const int nclusters) {
   using Cfg = TpGemmCfg<kCtaGroup, kBlockN, kSplit>;
   static_assert(!kSplit || kF32, "the hi/lo split exists for fp32 only");
+  static_assert(kPairs == 1 || (kPairs == 2 && kCtaGroup == 2 && !kSplit), "two pairs need cta_group 2");
+  constexpr int kClusterCtas = kCtaGroup * kPairs;
   constexpr int kElem = kF32 ? 4 : 2;                 // bytes per element
   constexpr int kRowElems = 128 / kElem;              // elements per 128-byte swizzle row
   constexpr int kKPerStage = kRowElems;               // k elements per pipeline stage
@@ -632,9 +643,12 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
   const int nwarps = static_cast<int>(blockDim.x >> 5);
   const int n_aux = 2 + (nwarps - 8);                         // warps 2, 3, 8..
   const int aux = warp == 2 ? 0 : warp == 3 ? 1 : warp >= 8 ? warp - 6 : -1;
-  const uint32_t cta_rank = kCtaGroup == 2 ? cluster_ctarank() : 0u;
-  const int cta = cluster * kCtaGroup + static_cast<int>(cta_rank);
-  const int nctas = nclusters * kCtaGroup;
+  const uint32_t cluster_rank = kClusterCtas > 1 ? cluster_ctarank() : 0u;   // 0 .. kClusterCtas-1
+  const uint32_t cta_rank = cluster_rank & static_cast<uint32_t>(kCtaGroup - 1);   // rank in the MMA pair
+  const uint32_t pair = kCtaGroup == 2 ? cluster_rank >> 1 : 0u;             // which pair of the cluster
+  const uint32_t leader_rank = cluster_rank & ~1u;                           // even CTA of this pair
+  const int cta = cluster * kClusterCtas + static_cast<int>(cluster_rank);
+  const int nctas = nclusters * kClusterCtas;
   const bool bf16 = ((p.idesc >> 7) & 7u) == 1u;
 
   // ------------------------------------------------------------------ setup
@@ -646,7 +660,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < 8; ++s) {
       mbar_init(bar_full + s * 8, 1);
-      mbar_init(bar_empty + s * 8, 1);
+      mbar_init(bar_empty + s * 8, kPairs);                   // one commit per pair that read it
       mbar_init(bar_split + s * 8, 4 * kCtaGroup);            // one arrival per split warp
     }
     for (int a = 0; a < 2; ++a) {
@@ -661,17 +675,17 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     tmem_relinquish<kCtaGroup>();
   }
   tc_fence_before();
-  if constexpr (kCtaGroup == 2) cluster_sync(); else __syncthreads();
+  if constexpr (kClusterCtas > 1) cluster_sync(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
-  const int num_tiles = p.num_m_blocks * p.num_n_blocks;
+  const int num_tiles = p.num_m_blocks * p.sched_n_blocks;
 
   if (warp == 0 && lane == 0) {
     // -------------------------------------------------------- TMA producer
     const int chunks_per_part = p.mblks_per_part / p.chunk_mblks;
     const uint32_t chunk_target = p.epoch * ((p.chunk_bytes + kPushUnit - 1) / kPushUnit);
-    const uint32_t full_leader = kCtaGroup == 2 ? mapa(bar_full, 0) : bar_full;
+    const uint32_t full_leader = kCtaGroup == 2 ? mapa(bar_full, leader_rank) : bar_full;
     int stage = 0;
     uint32_t phase = 0;
     Tracer<kTrace> tr(p, cta, 0);
@@ -687,7 +701,8 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         tr.ev(kEvFlagWaited, static_cast<uint32_t>(t));
       }
       const int m0 = tc.m_blk * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
-      const int n0 = tc.n_blk * kBlockN + static_cast<int>(cta_rank) * Cfg::kLoadN;
+      const int n0 = (tc.n_blk * kPairs + static_cast<int>(pair)) * kBlockN +
+                     static_cast<int>(cta_rank) * Cfg::kLoadN;
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
         mbar_wait(bar_empty + stage * 8, phase ^ 1u);
         uint8_t* sa = smem_ops + stage * Cfg::kStageBytes;
@@ -699,7 +714,15 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         else if (kCtaGroup == 1 || cta_rank == 0)
           mbar_arrive_expect_tx(bar_full + stage * 8, Cfg::kStageOps * kCtaGroup);
         const uint32_t fb = (kSplit ? bar_full : full_leader) + stage * 8;
-        tma_load_2d<kCtaGroup>(smem_u32(sa), &p.tmA, fb, kb * kKPerStage, m0);
+        if constexpr (kPairs == 2) {
+          // this CTA fetches HALF of its 128 A rows and multicasts them to the CTA with the same
+          // rank in the other pair (the other half comes from there): A crosses L2 -> SM once
+          const uint16_t mask = static_cast<uint16_t>((1u << cta_rank) | (1u << (2u + cta_rank)));
+          tma_load_2d_multicast(smem_u32(sa) + pair * (Cfg::kStageA / 2), &p.tmA, fb, kb * kKPerStage,
+                                m0 + static_cast<int>(pair) * (kBlockM / 2), mask);
+        } else {
+          tma_load_2d<kCtaGroup>(smem_u32(sa), &p.tmA, fb, kb * kKPerStage, m0);
+        }
         if constexpr (kBNMajor)
           tma_load_3d<kCtaGroup>(smem_u32(sb), &p.tmB, fb, 0, kb * kKPerStage, n0 / kRowElems);
         else
@@ -745,10 +768,13 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
             umma_f16<kCtaGroup>(tmem_d, ak, bk, p.idesc, static_cast<uint32_t>((kb | k) != 0));
           }
         }
-        umma_commit<kCtaGroup>(bar_empty + stage * 8);     // smem slot reusable when MMAs retire
+        // smem slot reusable when the MMAs retire: every CTA of the cluster hears it (with two
+        // pairs a CTA's slot is also written by the other pair's multicast)
+        umma_commit<kCtaGroup>(bar_empty + stage * 8, static_cast<uint16_t>((1u << kClusterCtas) - 1u));
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
-      umma_commit<kCtaGroup>(bar_tfull + acc * 8);         // accumulator ready for the epilogue
+      umma_commit<kCtaGroup>(bar_tfull + acc * 8,          // accumulator ready: this pair's epilogues
+                             static_cast<uint16_t>(0x3u << leader_rank));
       tr.ev(kEvTileIssued, static_cast<uint32_t>(t));
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
@@ -822,7 +848,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     // -------------------------------------------------------- epilogue
     const int q = warp & 3;                                 // TMEM lane quadrant
     uint8_t* ebuf = smem_epi + q * 2 * kEpiBufBytes;
-    const uint32_t tempty_leader = kCtaGroup == 2 ? mapa(bar_tempty, 0) : bar_tempty;
+    const uint32_t tempty_leader = kCtaGroup == 2 ? mapa(bar_tempty, leader_rank) : bar_tempty;
     int buf = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -833,7 +859,8 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
       const TileCoord tc = tile_coord(p, t);
       const int row_cta = tc.m_blk * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
       const int row0 = row_cta + q * 32;
-      const int n0 = tc.n_blk * kBlockN;
+      const int n_blk = tc.n_blk * kPairs + static_cast<int>(pair);
+      const int n0 = n_blk * kBlockN;
       mbar_wait(bar_tfull + acc * 8, acc_phase);
       tc_fence_after();
       tr.ev(kEvAccReady, static_cast<uint32_t>(t));
@@ -845,8 +872,8 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         // row inside the owner's shard; staging slot [parity][src] at the owner (push) or
         // [parity][owner] locally (pull)
         out_row = row0 - tc.part * p.part_rows;
-        cta_tile = ((row_cta - tc.part * p.part_rows) / kBlockM) * p.num_n_blocks + tc.n_blk;
-        const size_t slot_bytes = static_cast<size_t>(p.part_rows) * pitch;
+        cta_tile = ((row_cta - tc.part * p.part_rows) / kBlockM) * p.num_n_blocks + n_blk;
+        const size_t slot_bytes = static_cast<size_t>(p.rs_tiles) * (4 * (kBlockN / kRowElems)) * kEpiBufBytes;
         rs_dst = p.rs_transport == kRsPush
                      ? p.stage_base[tc.part] + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes
                      : p.stage_base[p.rank] + (static_cast<size_t>(parity) * p.world + tc.part) * slot_bytes;
@@ -899,7 +926,10 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         const int colb = col0 * kElem;
         if (p.mode == kModeRS) {
           __syncwarp();
-          store_chunk_st128<false>(rs_dst, pitch, out_row, colb, static_cast<int>(pitch), sbase, lane);
+          // unit-major staging: this chunk is unit (cta_tile, q, c), 4 KiB contiguous
+          store_chunk_st128<false>(rs_dst + (static_cast<size_t>(cta_tile * 4 + q) * (kBlockN / kRowElems) + c) *
+                                                kEpiBufBytes,
+                                   128, 0, 0, 128, sbase, lane);
           __syncwarp();            // every lane has read the staged rows before they are reused
         } else if (p.mode == kModeAGAfter && p.epi_transport == kEpiMulticast) {
           __syncwarp();
@@ -969,30 +999,33 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
   // ---------------------------------------------------------------- teardown
   __syncwarp();
   tc_fence_before();
-  if constexpr (kCtaGroup == 2) cluster_sync(); else __syncthreads();
+  if constexpr (kClusterCtas > 1) cluster_sync(); else __syncthreads();
   if (warp == 2) tmem_dealloc<kCtaGroup>(tmem_base, Cfg::kTmemCols);
 }
 
 // One rank per process / GPU: parameters in the kernel parameter space.
 template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kSplit = false,
-          bool kTrace = false>
+          bool kTrace = false, int kPairs = 1>
 __global__ void __launch_bounds__(kMaxThreads, 1)
 tp_gemm_kernel(const __grid_constant__ TpGemmParams p) {
-  const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
-  const int nclusters = kCtaGroup == 2 ? static_cast<int>(num_clusters_x()) : static_cast<int>(gridDim.x);
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kSplit, kTrace>(p, cluster, nclusters);
+  constexpr bool kClustered = kCtaGroup * kPairs > 1;
+  const int cluster = kClustered ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
+  const int nclusters = kClustered ? static_cast<int>(num_clusters_x()) : static_cast<int>(gridDim.x);
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kSplit, kTrace, kPairs>(p, cluster, nclusters);
 }
 
 // Several ranks emulated by ONE launch on one GPU (tests): the grid is split into
 // `world` equal groups of clusters, group r runs rank r's parameter block. All
 // CTAs of one launch are co-resident (grid <= SM count), so ranks that wait on
 // each other make progress, which separate launches on one GPU cannot guarantee.
-template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kSplit = false>
+template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kSplit = false,
+          int kPairs = 1>
 __global__ void __launch_bounds__(kMaxThreads, 1)
 tp_gemm_emulated_kernel(const TpGemmParams* __restrict__ plist, int clusters_per_rank) {
-  const int cluster = kCtaGroup == 2 ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
+  constexpr bool kClustered = kCtaGroup * kPairs > 1;
+  const int cluster = kClustered ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
   const int vr = cluster / clusters_per_rank;
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kSplit, false>(
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kSplit, false, kPairs>(
       plist[vr], cluster - vr * clusters_per_rank, clusters_per_rank);
 }
 

@@ -87,7 +87,8 @@ class TpGemmPlan:
 def _base_config(mode: int, dtype, m: int, n: int, k: int, rank: int, world: int,
                  b_layout: int, cta_group: int, block_n: int, group_m: int, num_sms: int,
                  chunk_rows: int = 0, fp32_mode: str = "3xtf32",
-                 unrotated: bool = False, activation: Optional[str] = None) -> N.TpGemmConfig:
+                 unrotated: bool = False, activation: Optional[str] = None,
+                 cluster_pairs: int = 0) -> N.TpGemmConfig:
     if fp32_mode not in FP32_MODES:
         raise ValueError(f"fp32_mode must be one of {sorted(FP32_MODES)}, got {fp32_mode!r}")
     if activation not in ACTIVATIONS:
@@ -99,13 +100,15 @@ def _base_config(mode: int, dtype, m: int, n: int, k: int, rank: int, world: int
     cfg.fp32_mode = FP32_MODES[fp32_mode]
     cfg.unrotated = 1 if unrotated else 0
     cfg.epilogue_act = ACTIVATIONS[activation]
+    cfg.cluster_pairs = int(cluster_pairs)
     cfg.m, cfg.n, cfg.k = m, n, k
     return cfg
 
 
 def plain_gemm_plan(a, b, out=None, *, b_is_nk: bool = False, cta_group: int = 0,
                     block_n: int = 0, group_m: int = 0, num_sms: int = 0,
-                    fp32_mode: str = "3xtf32", activation: Optional[str] = None):
+                    fp32_mode: str = "3xtf32", activation: Optional[str] = None,
+                    cluster_pairs: int = 0):
     """Plan for ``out[m,n] = a[m,k] @ b`` with ``b`` ``[k,n]`` (or ``[n,k]`` if ``b_is_nk``)."""
     import torch
     assert a.is_cuda and b.is_cuda and a.is_contiguous() and b.is_contiguous()
@@ -118,7 +121,7 @@ def plain_gemm_plan(a, b, out=None, *, b_is_nk: bool = False, cta_group: int = 0
     b, b_is_nk = _weight_for_kernel(b, b_is_nk)
     cfg = _base_config(N.MODE_PLAIN, a.dtype, m, n, k, 0, 1, N.B_NK if b_is_nk else N.B_KN,
                        cta_group, block_n, group_m, num_sms, fp32_mode=fp32_mode,
-                       activation=activation)
+                       activation=activation, cluster_pairs=cluster_pairs)
     cfg.a, cfg.b = a.data_ptr(), b.data_ptr()
     cfg.out[0] = out.data_ptr()
     return TpGemmPlan(cfg, keepalive=(a, b, out)), out
@@ -191,7 +194,8 @@ class FusedAllGatherGemm(_FusedBase):
                  cta_group: int = 0, block_n: int = 0, group_m: int = 0, num_sms: int = 0,
                  b_is_nk: bool = False, transport: str = "auto", trace: bool = False,
                  fp32_mode: str = "3xtf32", unrotated: bool = False,
-                 activation: Optional[str] = None, out=None, comm_warps: int = 0):
+                 activation: Optional[str] = None, out=None, comm_warps: int = 0,
+                 cluster_pairs: int = 0):
         super().__init__(heap, rank, world)
         import torch
         if m % world:
@@ -200,7 +204,8 @@ class FusedAllGatherGemm(_FusedBase):
         self.order = order
         b, b_is_nk = _weight_for_kernel(b, b_is_nk)
         layout = N.B_NK if b_is_nk else N.B_KN
-        common = dict(fp32_mode=fp32_mode, unrotated=unrotated, activation=activation)
+        common = dict(fp32_mode=fp32_mode, unrotated=unrotated, activation=activation,
+                      cluster_pairs=cluster_pairs)
         if out is not None and order != "AG_before":
             raise ValueError("a caller-provided output is supported for order='AG_before' only")
         if order == "AG_before":
@@ -313,7 +318,8 @@ class FusedGemmReduceScatter(_FusedBase):
     def __init__(self, heap, rank: int, world: int, m: int, n: int, k: int, dtype, a, b,
                  chunk_rows: int = 0, cta_group: int = 0, block_n: int = 0, group_m: int = 0,
                  num_sms: int = 0, b_is_nk: bool = False, trace: bool = False,
-                 transport: str = "auto", fp32_mode: str = "3xtf32", unrotated: bool = False):
+                 transport: str = "auto", fp32_mode: str = "3xtf32", unrotated: bool = False,
+                 cluster_pairs: int = 0):
         super().__init__(heap, rank, world)
         import torch
         self.trace_buf = None
@@ -330,13 +336,15 @@ class FusedGemmReduceScatter(_FusedBase):
         self.transport = _resolve_transport(transport, RS_TRANSPORTS, "push", heap, "tp_rowwise")
         if world == 1:
             cfg = _base_config(N.MODE_PLAIN, dtype, m, n, k, 0, 1, layout, cta_group, block_n,
-                               group_m, num_sms, fp32_mode=fp32_mode)
+                               group_m, num_sms, fp32_mode=fp32_mode, cluster_pairs=cluster_pairs)
             cfg.out[0] = self.out.data_ptr()
         else:
-            st_off, self.staging = heap.empty((2, world, rows, n), dtype)
+            # staging is unit-major and covers whole 256-column blocks (see rs_reduce_loop)
+            n_pad = (n + 255) // 256 * 256
+            st_off, self.staging = heap.empty((2, world, rows, n_pad), dtype)
             cfg = _base_config(N.MODE_RS, dtype, m, n, k, rank, world, layout, cta_group, block_n,
                                group_m, num_sms, chunk_rows, fp32_mode=fp32_mode,
-                               unrotated=unrotated)
+                               unrotated=unrotated, cluster_pairs=cluster_pairs)
             cfg.rs_transport = RS_TRANSPORTS[self.transport]
             for p in range(world):
                 cfg.stage[p] = heap.ptr(st_off, p)

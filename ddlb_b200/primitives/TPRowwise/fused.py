@@ -65,7 +65,7 @@ class FusedTPRowwise(TPRowwise):
             chunk_rows = rows // s
         heap = None
         if d > 1:
-            heap = comm.symmetric_heap(2 * self.m * self.n * self.A.element_size() + (64 << 20))
+            heap = comm.symmetric_heap(2 * self.m * ((self.n + 255) // 256 * 256) * self.A.element_size() + (64 << 20))
         self.op = FusedGemmReduceScatter(
             heap, comm.rank, d, self.m, self.n, self.k, self.torch_dtype, self.A, self.B,
             chunk_rows=chunk_rows, cta_group=int(self.options["cta_group"]),

@@ -124,8 +124,10 @@ typedef struct ddlb_tp_gemm_config {
   int32_t fp32_mode;     /* DDLB_FP32_* */
   int32_t epilogue_act;  /* DDLB_ACT_*: applied to the fp32 accumulator before the output is
                           * rounded (PLAIN / AG_*; not on tp_rowwise partial sums) */
-  int32_t comm_warps;    /* AG_BEFORE: aux warps per CTA that move data, 0 = all (6) */
-  int32_t reserved;
+  int32_t comm_warps;    /* AG_BEFORE: aux warps per CTA that move data, 0 = auto (2 for pull) */
+  int32_t cluster_pairs; /* 2: clusters of four CTAs = two MMA pairs on neighbouring n-blocks, the A
+                          * tile multicast to both (fp16/bf16, cta_group 2, block_n 256, even
+                          * number of n-blocks); 0 / 1: one pair per cluster */
   int64_t m, n, k;       /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
   /* PLAIN:     a = A[m,k]                 out[rank] = C[m,n]
    * AG_BEFORE: a = gathered A[m,k] (own shard rows already in place), peer_a[r] = rank r's

@@ -42,6 +42,7 @@ def main():
     ap.add_argument("--dtypes", default="bfloat16,float16")
     ap.add_argument("--perf", action="store_true")
     ap.add_argument("--fp32-mode", default="3xtf32", choices=["3xtf32", "tf32"])
+    ap.add_argument("--cluster-pairs", type=int, default=0)
     args = ap.parse_args()
     torch.manual_seed(0)
     ok_all = True
@@ -55,7 +56,7 @@ def main():
             try:
                 plan, out = plain_gemm_plan(a, b, b_is_nk=args.b_layout == "nk",
                                             cta_group=args.cta_group, block_n=args.block_n,
-                                            fp32_mode=args.fp32_mode)
+                                            fp32_mode=args.fp32_mode, cluster_pairs=args.cluster_pairs)
             except Exception as exc:
                 print(f"[{dt_name} {shp}] plan failed: {exc}")
                 ok_all = False
@@ -70,7 +71,7 @@ def main():
             bad = int((~(err <= tol)).sum())
             status = "OK " if bad == 0 else "BAD"
             ok_all &= bad == 0
-            line = (f"[{status}] g={args.cta_group} bn={args.block_n} b={args.b_layout} {dt_name} {shp} "
+            line = (f"[{status}] g={args.cta_group} bn={args.block_n} pairs={args.cluster_pairs} b={args.b_layout} {dt_name} {shp} "
                     f"max_err={err.max().item():.4g} bad={bad}/{err.numel()} info={plan.info}")
             if bad:
                 idx = (~(err <= tol)).nonzero()[:6].tolist()

@@ -38,10 +38,10 @@ def main():
     mc = getattr(heap, "has_multicast", False)
     if r == 0:
         print(f"world {d} heap {type(heap).__name__} multicast {mc}", flush=True)
-    for n in (64, 1024):
+    for n in ((1024,) if os.environ.get("DDLB_AB_QUICK", "0") == "1" else (64, 1024)):
         b = torch.randn(k, n, device=comm.device, dtype=dt)
         cases = [("AG_before", "pull", w) for w in (2, 4, 6)]
-        cases += [("AG_before", t, 0) for t in ["push"] + (["multimem"] if mc else [])]
+        cases += [("AG_before", t, w) for t in ["push"] + (["multimem"] if mc else []) for w in (2, 6)]
         cases += [("AG_after", t, 0) for t in ["tma", "st128"] + (["multimem"] if mc else [])]
         for order, transport, warps in cases:
             moved = (d - 1) / d * m * (k if order == "AG_before" else n) * 2

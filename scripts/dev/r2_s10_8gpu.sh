@@ -6,7 +6,11 @@ mkdir -p gpurun_out
 export DDLB_STORE_TIMEOUT=120
 {
 echo "=== 1. multi-GPU suite at world $N"
-timeout 600 python -m pytest tests/test_multigpu.py -x -q -k "$N" 2>&1 | tail -8
+if [ "${DDLB_SESSION_QUICK:-0}" = "1" ]; then
+  timeout 300 python -m pytest tests/test_multigpu.py -x -q -k "(slow_rank or rowwise_fused) and $N" 2>&1 | tail -5
+else
+  timeout 600 python -m pytest tests/test_multigpu.py -x -q -k "$N" 2>&1 | tail -8
+fi
 echo "=== 2. bench ours N=$N"
 timeout 400 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29541 bench.py --gpus $N --steps 50 --warmup 10 2>gpurun_out/bench_ours_$N.err | tee gpurun_out/bench_ours_n$N.json | cut -c1-400
 tail -3 gpurun_out/bench_ours_$N.err | cut -c1-300

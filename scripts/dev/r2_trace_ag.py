@@ -73,7 +73,7 @@ def main():
     m2, n2, k2, dt2 = 8192, 1024, 8192, torch.float16
     a = (2 * torch.rand(m2, k2 // d, device=comm.device) - 1).to(dt2)
     b = (2 * torch.rand(k2 // d, n2, device=comm.device) - 1).to(dt2)
-    for transport in ("push",):
+    for transport in ("push",) + (("multimem",) if getattr(heap, "has_multicast", False) else ()):
         op = FusedGemmReduceScatter(heap, r, d, m2, n2, k2, dt2, a, b, transport=transport, trace=True,
                                     cta_group=2, block_n=256)
         torch.cuda.synchronize()

@@ -67,3 +67,29 @@ def test_unsupported_shapes_fail_loudly():
     cfg.m, cfg.n, cfg.k = 128, 128, 64
     assert N.lib().ddlb_tp_gemm_sig_words(ctypes.byref(cfg)) < 0
     assert "[n,k]" in N.lib().ddlb_last_error().decode()
+
+
+@pytest.mark.parametrize("b_is_nk", [False, True])
+@pytest.mark.parametrize("shape", [(256, 512, 64), (1024, 1024, 1024), (2304, 1536, 4096), (8192, 2048, 512),
+                                   (512, 1000, 200)])
+def test_two_pair_clusters_multicast_a(shape, b_is_nk):
+    """Clusters of four CTAs: two MMA pairs on neighbouring n-blocks, A multicast to both."""
+    import torch
+    from ddlb_b200.ops.tp_gemm import plain_gemm_plan
+    torch.manual_seed(4)
+    m, n, k = shape
+    a = torch.randn(m, k, device="cuda", dtype=torch.bfloat16)
+    b_kn = torch.randn(k, n, device="cuda", dtype=torch.bfloat16)
+    if not b_is_nk and n % 64:
+        pytest.skip("B [k,n] needs n % 64 == 0")
+    b = b_kn.t().contiguous() if b_is_nk else b_kn
+    plan, out = plain_gemm_plan(a, b, b_is_nk=b_is_nk, cta_group=2, block_n=256, cluster_pairs=2)
+    assert plan.info["cluster"] == 2 and plan.info["grid"] % 4 == 0
+    for _ in range(2):
+        out.fill_(float("nan"))
+        plan.run()
+        torch.cuda.synchronize()
+        ref = a.float() @ b_kn.float()
+        err = (out.float() - ref).abs()
+        tol = 2e-2 * (k ** 0.5) + 1e-2 * ref.abs()
+        assert int((~(err <= tol)).sum()) == 0, f"max err {err.max().item()}"
