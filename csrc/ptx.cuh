@@ -185,6 +185,11 @@ __device__ __forceinline__ void st_release_gpu(uint32_t* p, uint32_t v) {
 __device__ __forceinline__ void red_add_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+// Flag bump WITHOUT a fence of its own: the caller has already fenced (a release-qualified red
+// compiles to MEMBAR + RED, and MEMBAR.SYS alone was measured at ~5 us with 4 ranks).
+__device__ __forceinline__ void red_add_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ void red_add_release_gpu(uint32_t* p, uint32_t v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -200,12 +205,14 @@ __device__ __forceinline__ uint32_t ld_relaxed_gpu(const uint32_t* p) {
   return v;
 }
 
-// Spin until *p >= target (wrap-safe signed compare), system or gpu scope.
+// Spin until *p >= target (wrap-safe signed compare); kSys: the flag is written by another GPU.
 // The poll is a RELAXED load and the acquire is ONE fence after the flag has been seen: an
 // acquire load compiles to LDG.STRONG + CCTL.IVALL, and a spinning warp then invalidates its
-// SM's whole L1 on every poll - with a producer lane spinning on every SM that throttled the
-// peer loads of the comm warps (round 2: the in-kernel all-gather ran at ~390 GB/s where a
-// plain copy kernel moves 620-740 GB/s).
+// SM's whole L1 on every poll. The closing fence is GPU scope in both cases: whatever a peer
+// wrote before it raised the flag was fenced at system scope on ITS side and therefore sits
+// in this GPU's L2 by the time the flag is visible; what this SM still has to do is drop
+// stale L1 lines and order its later loads (MEMBAR.GPU + CCTL.IVALL). A system-scope fence
+// here costs ~5 us per wait (device trace, 4 ranks) and buys nothing.
 template <bool kSys>
 __device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t target) {
   uint64_t t0 = 0;
@@ -221,7 +228,7 @@ __device__ __forceinline__ void wait_flag_ge(const uint32_t* p, uint32_t target)
         die(kErrFlagTimeout, static_cast<uint32_t>(reinterpret_cast<uintptr_t>(p)), target);
     }
   }
-  if (kSys) fence_acq_rel_sys(); else fence_acq_rel_gpu();
+  fence_acq_rel_gpu();
 }
 
 // ---------------------------------------------------------------------------
