@@ -818,9 +818,10 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     // -------------------------------------------------------- comm warps (every CTA)
     if (cta == 0 && aux == 1 && lane < p.world && lane != p.rank)
       st_release_sys(p.sig_peer[lane] + kSigReady + p.rank, p.epoch);   // my previous launch is over
-    // pull: 2 warps per CTA fill the links, more oversubscribe them (see comm_warp_pull);
-    // warps 8.. split operands in 3xTF32
-    int na = (kSplit || p.ag_transport == kAgPull) ? 2 : n_aux;
+    // 2 warps per CTA fill the links, more oversubscribe them (see comm_warp_pull; push and
+    // multimem.st behave the same: 213 vs 240 us and 320 vs 352 us at 2 ranks); warps 8.. split
+    // operands in 3xTF32
+    int na = 2;                                              // every transport: measured, see above
     if (p.comm_warps > 0) na = p.comm_warps < n_aux ? p.comm_warps : n_aux;
     if (kSplit && na > 2) na = 2;
     if (cta == 0 && aux == 0 && lane == 0) p.sig_local[kSigClaim + ((p.epoch & 1u) ^ 1u)] = 0u;
