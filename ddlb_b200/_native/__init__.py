@@ -61,9 +61,17 @@ def lib() -> ctypes.CDLL:
             from . import build as _build
             if _build.is_stale():
                 _build.build()
-        except Exception as exc:  # no nvcc on the box: use the shipped .so if present
+        except Exception as exc:  # no nvcc on the box, or a compile error
             if not os.path.exists(LIB_PATH):
                 raise NativeError(f"libddlb_b200.so is missing and could not be built: {exc}")
+            # an OLD library would run old kernels (or miss new symbols) without a word
+            if os.environ.get("DDLB_ALLOW_STALE_LIB", "0") != "1":
+                raise NativeError(
+                    "csrc/ or include/ changed since libddlb_b200.so was built and the rebuild "
+                    f"failed ({str(exc).splitlines()[0][:200]}); fix the build or set "
+                    "DDLB_ALLOW_STALE_LIB=1 to load the stale library") from exc
+            import warnings
+            warnings.warn(f"loading a STALE libddlb_b200.so (rebuild failed: {exc})")
     if not os.path.exists(LIB_PATH):
         raise NativeError(
             f"{LIB_PATH} not found; run `python -m ddlb_b200._native.build` (needs nvcc)")
