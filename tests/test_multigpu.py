@@ -116,3 +116,16 @@ def test_barrier_stress_epoch_wrap(world, tmp_path):
                           timeout=400)
     assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
     assert proc.stdout.count("barrier stress ok") == world
+
+
+@pytest.mark.parametrize("world", [2, 8])
+def test_tp_mlp_block_on_real_ranks(world):
+    """TPMLP.forward with changing activations, two launches per pass, vs an fp32 reference."""
+    if _ngpus() < world:
+        pytest.skip(f"needs {world} GPUs")
+    script = os.path.join(ROOT, "tests", "helpers", "tp_mlp_ranks.py")
+    proc = subprocess.run([sys.executable, "-m", "ddlb_b200.launcher", "-np", str(world), "--timeout",
+                           "300", "--all-output", script], cwd=ROOT, capture_output=True, text=True,
+                          timeout=400)
+    assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
+    assert proc.stdout.count("tp-mlp ok") == world
