@@ -314,6 +314,26 @@ extern "C" int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_
   if (int rc = resolve(normalized, r)) return rc;
   const ddlb_tp_gemm_config& c = normalized;
   if (c.a == nullptr || c.b == nullptr || c.out[c.rank] == nullptr) return set_error("null a/b/out pointer");
+  if (r.pairs == 2) {
+    // The A tile is fetched with a TMA multicast load. TMA multicast loads here read only this
+    // GPU's memory, since on B200 a TMA multicast load from another GPU's memory hung the GPU:
+    // refuse an A operand that is not resident on the current device (first and last byte).
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) { (void)cudaGetLastError(); return set_error("cluster_pairs=2: no current device"); }
+    const size_t a_bytes = static_cast<size_t>(r.a_rows) * static_cast<size_t>(r.kk) * r.elem;
+    const char* ends[2] = {static_cast<const char*>(c.a), static_cast<const char*>(c.a) + a_bytes - 1};
+    for (const char* q : ends) {
+      cudaPointerAttributes attr;
+      cudaError_t e = cudaPointerGetAttributes(&attr, q);
+      if (e != cudaSuccess || attr.type != cudaMemoryTypeDevice || attr.device != dev) {
+        (void)cudaGetLastError();
+        return set_error("cluster_pairs=2 multicasts the A tile and needs A in the current device's own "
+                         "memory (device %d); got memory of type %d on device %d", dev,
+                         e == cudaSuccess ? static_cast<int>(attr.type) : -1,
+                         e == cudaSuccess ? attr.device : -1);
+      }
+    }
+  }
   if (c.world > 1 && c.mode != DDLB_MODE_PLAIN) {
     if (c.sig_local == nullptr) return set_error("sig_local is required for fused modes");
     for (int p = 0; p < c.world; ++p) {

@@ -3,7 +3,7 @@
 Importing this package touches neither CUDA nor the native library: heavy
 symbols resolve lazily (PEP 562), as in the reference (``ddlb/__init__.py:25-30``).
 """
-__version__ = "0.1.0"
+__version__ = "0.2.0"
 
 _LAZY = {
     "PrimitiveBenchmarkRunner": ("ddlb_b200.benchmark", "PrimitiveBenchmarkRunner"),

@@ -127,7 +127,9 @@ typedef struct ddlb_tp_gemm_config {
   int32_t comm_warps;    /* AG_BEFORE: aux warps per CTA that move data, 0 = auto (2 for pull) */
   int32_t cluster_pairs; /* 2: clusters of four CTAs = two MMA pairs on neighbouring n-blocks, the A
                           * tile multicast to both (fp16/bf16, cta_group 2, block_n 256, even
-                          * number of n-blocks); 0 / 1: one pair per cluster */
+                          * number of n-blocks); 0 / 1: one pair per cluster. `a` must then be
+                          * memory of the current device itself (checked): TMA multicast loads
+                          * here read only this GPU's memory */
   int64_t m, n, k;       /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
   /* PLAIN:     a = A[m,k]                 out[rank] = C[m,n]
    * AG_BEFORE: a = gathered A[m,k] (own shard rows already in place), peer_a[r] = rank r's

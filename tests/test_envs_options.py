@@ -98,4 +98,4 @@ def test_lazy_import_does_not_load_torch_cuda_or_native():
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True,
                          cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     assert out.returncode == 0, out.stderr
-    assert out.stdout.strip() == "0.1.0"
+    assert out.stdout.strip() == "0.2.0"
