@@ -5,6 +5,7 @@
 //        -Iinclude csrc/ddlb_b200.cu -o ddlb_b200/_native/libddlb_b200.so
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 

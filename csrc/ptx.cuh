@@ -89,6 +89,15 @@ __device__ __forceinline__ void cluster_sync() {
   cluster_wait();
 }
 
+// Programmatic dependent launch: `griddep_launch_dependents` lets the next kernel of the stream
+// (launched with programmatic stream serialization) start its CTAs as soon as SMs free up;
+// `griddep_wait` blocks until the previous kernel has completed and its writes are visible.
+// Both are no-ops in a kernel that was launched without the attribute.
+__device__ __forceinline__ void griddep_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // Map a local shared::cta address to the same offset in CTA `rank` of the cluster.
 __device__ __forceinline__ uint32_t mapa(uint32_t saddr, uint32_t rank) {
   uint32_t out;

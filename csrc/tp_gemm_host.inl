@@ -105,8 +105,6 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
       return set_error("cluster_pairs=2 needs fp16/bf16, cta_group=2, block_n=256 and an even number "
                        "of 256-column blocks (n = %lld)", (long long)c.n);
   }
-  const int cluster_ctas = r.cta_group * r.pairs;
-
   int dev = 0, sms = 0;
   if (cudaGetDevice(&dev) != cudaSuccess ||
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) {
@@ -116,6 +114,17 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
     sms = c.num_sms;
   }
   r.grid = c.num_sms > 0 ? (c.num_sms < sms ? c.num_sms : sms) : sms;
+  // Small single-rank problems with the tile shape left on auto: a 256x256 tile per CTA pair
+  // leaves most SMs idle when there are far fewer tiles than clusters, and both the main loop and
+  // the (exposed) epilogue of the only wave scale with the tile. Halve it (BLOCK_N 128: every CTA
+  // of a pair computes 128x128) while one wave still holds all tiles. Measured at 1024^3: 16 tiles
+  // on 32 SMs took 13.8 us against cuBLAS' 8.5 us.
+  if (c.mode == DDLB_MODE_PLAIN && c.cta_group == 0 && c.block_n == 0 && r.pairs == 1 && r.elem == 2 &&
+      c.n > 128) {
+    const int64_t mb256 = (c.m + 255) / 256, nb128 = (c.n + 127) / 128;
+    if (mb256 * nb128 <= r.grid / 2) r.block_n = 128;
+  }
+  const int cluster_ctas = r.cta_group * r.pairs;
   r.grid -= r.grid % cluster_ctas;
   if (r.grid < cluster_ctas) return set_error("no SMs to launch on");
 
@@ -146,6 +155,7 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
   if (c.epi_transport < 0 || c.epi_transport > 2) return set_error("bad epi_transport %d", c.epi_transport);
   if (c.rs_transport < 0 || c.rs_transport > 2) return set_error("bad rs_transport %d", c.rs_transport);
   if (c.epilogue_act < 0 || c.epilogue_act > 3) return set_error("bad epilogue_act %d", c.epilogue_act);
+  if (c.pdl < 0 || c.pdl > 2) return set_error("pdl must be 0 (auto), 1 (on) or 2 (off), got %d", c.pdl);
   if (c.epilogue_act != 0 && c.mode == DDLB_MODE_RS && c.world > 1)
     return set_error("an epilogue activation cannot be applied to partial sums (tp_rowwise)");
 
@@ -287,6 +297,13 @@ static void fill_schedule(TpGemmParams& p, const ddlb_tp_gemm_config& c, const R
   p.epi_transport = c.epi_transport;
   p.rs_transport = c.rs_transport;
   p.act = c.epilogue_act;
+  {
+    // programmatic dependent launch: auto = single-rank plans only (the multi-rank kernels wait for
+    // peers, and their overlap with the previous launch has not been measured on real NVLink)
+    const char* env = getenv("DDLB_PDL");
+    const bool env_off = env != nullptr && env[0] == '0';
+    p.pdl = (!env_off && (c.pdl == 1 || (c.pdl == 0 && c.world == 1))) ? 1 : 0;
+  }
   p.comm_warps = c.comm_warps;
 }
 }  // namespace ddlb
@@ -443,9 +460,14 @@ extern "C" int ddlb_tp_gemm_run(ddlb_tp_gemm_plan* plan, uint32_t epoch, void* s
   if (plan == nullptr) return set_error("null plan");
   plan->params.epoch = epoch;
   cudaLaunchConfig_t lc;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   fill_launch(lc, attr, static_cast<unsigned>(plan->res.grid), plan->res.threads, plan->smem_bytes,
               plan->res.cta_group * plan->res.pairs, static_cast<cudaStream_t>(stream));
+  if (plan->params.pdl) {
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    lc.numAttrs = 2;
+  }
   void* args[1] = {&plan->params};
   cudaError_t e = cudaLaunchKernelExC(&lc, reinterpret_cast<const void*>(plan->kernel), args);
   if (e != cudaSuccess) {

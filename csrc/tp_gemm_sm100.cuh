@@ -86,6 +86,7 @@ struct TpGemmParams {
   uint32_t epoch;
   int stages;             // operand ring depth actually used (<= Cfg::kStages)
   int act;                // epilogue activation on the final output (PLAIN / AG_*): kAct*
+  int pdl;                // launched with programmatic stream serialization (see griddep_wait)
   // AG_BEFORE
   int ag_transport;
   int comm_warps;                     // aux warps per CTA that move data (0 = all of them)
@@ -680,6 +681,12 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
   if constexpr (kClusterCtas > 1) cluster_sync(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  if (p.pdl) {
+    // everything above touched only shared memory, TMEM and the kernel parameters; from here on
+    // global memory is read and written, so the previous kernel of the stream must be complete
+    griddep_launch_dependents();
+    griddep_wait();
+  }
 
   const int num_tiles = p.num_m_blocks * p.sched_n_blocks;
 

@@ -41,7 +41,7 @@ class TpGemmConfig(Structure):
         ("rank", c_int32), ("world", c_int32), ("chunk_rows", c_int32),
         ("ag_transport", c_int32), ("epi_transport", c_int32), ("rs_transport", c_int32),
         ("unrotated", c_int32), ("fp32_mode", c_int32), ("epilogue_act", c_int32),
-        ("comm_warps", c_int32), ("cluster_pairs", c_int32),
+        ("comm_warps", c_int32), ("cluster_pairs", c_int32), ("pdl", c_int32),
         ("m", c_int64), ("n", c_int64), ("k", c_int64),
         ("a", c_void_p), ("b", c_void_p),
         ("out", c_void_p * MAX_WORLD), ("peer_a", c_void_p * MAX_WORLD),

@@ -88,7 +88,7 @@ def _base_config(mode: int, dtype, m: int, n: int, k: int, rank: int, world: int
                  b_layout: int, cta_group: int, block_n: int, group_m: int, num_sms: int,
                  chunk_rows: int = 0, fp32_mode: str = "3xtf32",
                  unrotated: bool = False, activation: Optional[str] = None,
-                 cluster_pairs: int = 0) -> N.TpGemmConfig:
+                 cluster_pairs: int = 0, pdl: Optional[bool] = None) -> N.TpGemmConfig:
     if fp32_mode not in FP32_MODES:
         raise ValueError(f"fp32_mode must be one of {sorted(FP32_MODES)}, got {fp32_mode!r}")
     if activation not in ACTIVATIONS:
@@ -101,6 +101,7 @@ def _base_config(mode: int, dtype, m: int, n: int, k: int, rank: int, world: int
     cfg.unrotated = 1 if unrotated else 0
     cfg.epilogue_act = ACTIVATIONS[activation]
     cfg.cluster_pairs = int(cluster_pairs)
+    cfg.pdl = 0 if pdl is None else (1 if pdl else 2)   # None: on for single-rank plans
     cfg.m, cfg.n, cfg.k = m, n, k
     return cfg
 
@@ -108,8 +109,12 @@ def _base_config(mode: int, dtype, m: int, n: int, k: int, rank: int, world: int
 def plain_gemm_plan(a, b, out=None, *, b_is_nk: bool = False, cta_group: int = 0,
                     block_n: int = 0, group_m: int = 0, num_sms: int = 0,
                     fp32_mode: str = "3xtf32", activation: Optional[str] = None,
-                    cluster_pairs: int = 0):
-    """Plan for ``out[m,n] = a[m,k] @ b`` with ``b`` ``[k,n]`` (or ``[n,k]`` if ``b_is_nk``)."""
+                    cluster_pairs: int = 0, pdl: Optional[bool] = None):
+    """Plan for ``out[m,n] = a[m,k] @ b`` with ``b`` ``[k,n]`` (or ``[n,k]`` if ``b_is_nk``).
+
+    ``pdl`` (default on): the launch uses programmatic stream serialization, so the kernel's
+    prologue overlaps the tail of the previous kernel of the stream; all global accesses still
+    wait for that kernel to complete."""
     import torch
     assert a.is_cuda and b.is_cuda and a.is_contiguous() and b.is_contiguous()
     assert a.dtype == b.dtype
@@ -121,7 +126,7 @@ def plain_gemm_plan(a, b, out=None, *, b_is_nk: bool = False, cta_group: int = 0
     b, b_is_nk = _weight_for_kernel(b, b_is_nk)
     cfg = _base_config(N.MODE_PLAIN, a.dtype, m, n, k, 0, 1, N.B_NK if b_is_nk else N.B_KN,
                        cta_group, block_n, group_m, num_sms, fp32_mode=fp32_mode,
-                       activation=activation, cluster_pairs=cluster_pairs)
+                       activation=activation, cluster_pairs=cluster_pairs, pdl=pdl)
     cfg.a, cfg.b = a.data_ptr(), b.data_ptr()
     cfg.out[0] = out.data_ptr()
     return TpGemmPlan(cfg, keepalive=(a, b, out)), out

@@ -130,7 +130,13 @@ typedef struct ddlb_tp_gemm_config {
                           * number of n-blocks); 0 / 1: one pair per cluster. `a` must then be
                           * memory of the current device itself (checked): TMA multicast loads
                           * here read only this GPU's memory */
-  int64_t m, n, k;       /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
+  int32_t pdl;           /* programmatic dependent launch: the kernel is launched with stream
+                          * serialization relaxed, so its prologue (barrier init, TMEM allocation,
+                          * tensor-map prefetch) runs while the previous kernel of the stream drains;
+                          * every global access still waits for that kernel (griddepcontrol.wait).
+                          * 0 = auto (on when world == 1), 1 = on, 2 = off; DDLB_PDL=0 in the
+                          * environment turns it off everywhere. No reference counterpart. */
+  int64_t m, n, k;      /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
   /* PLAIN:     a = A[m,k]                 out[rank] = C[m,n]
    * AG_BEFORE: a = gathered A[m,k] (own shard rows already in place), peer_a[r] = rank r's
    *            gathered buffer, out[rank] = C[m,n]; mc_ptr = multicast alias of the gathered A

@@ -93,3 +93,52 @@ def test_two_pair_clusters_multicast_a(shape, b_is_nk):
         err = (out.float() - ref).abs()
         tol = 2e-2 * (k ** 0.5) + 1e-2 * ref.abs()
         assert int((~(err <= tol)).sum()) == 0, f"max err {err.max().item()}"
+
+
+@pytest.mark.parametrize("pdl", [True, False])
+def test_programmatic_dependent_launch_orders_memory(pdl):
+    """Back-to-back launches with programmatic stream serialization: the kernel's prologue may run
+    early, but every read must see what the previous kernel of the stream wrote, whether that
+    kernel is a PyTorch one (the input changes before every launch) or our own (a chain of two
+    GEMMs where the second consumes the first one's output)."""
+    import torch
+    from ddlb_b200.ops.tp_gemm import plain_gemm_plan
+    torch.manual_seed(7)
+    m, n, k = 4096, 1024, 1024
+    a = torch.empty(m, k, device="cuda", dtype=torch.bfloat16)
+    b1 = (torch.randn(k, n, device="cuda") / k ** 0.5).bfloat16()
+    b2 = (torch.randn(n, n, device="cuda") / n ** 0.5).bfloat16()
+    plan1, h = plain_gemm_plan(a, b1, pdl=pdl)
+    plan2, out = plain_gemm_plan(h, b2, pdl=pdl)
+    inputs = [torch.randn(m, k, device="cuda").bfloat16() for _ in range(6)]
+    results = []
+    for x in inputs:                      # nothing synchronises inside this loop
+        a.copy_(x)
+        plan1.run()
+        plan2.run()
+        results.append(out.clone())
+        out.fill_(float("nan"))
+        h.fill_(float("nan"))
+    torch.cuda.synchronize()
+    for x, got in zip(inputs, results):
+        h_ref = (x.float() @ b1.float()).bfloat16()
+        _check(got, h_ref.float() @ b2.float(), n)
+
+
+@pytest.mark.parametrize("shape", [(1024, 1024, 1024), (2048, 1024, 512), (384, 320, 200), (4096, 1024, 256)])
+def test_auto_tile_shape(shape):
+    """Tile shape left on auto: small problems resolve to BLOCK_N 128 (one wave, more SMs busy)."""
+    import torch
+    from ddlb_b200.ops.tp_gemm import plain_gemm_plan
+    torch.manual_seed(3)
+    m, n, k = shape
+    a = torch.randn(m, k, device="cuda").bfloat16()
+    b = torch.randn(k, n, device="cuda").bfloat16()
+    plan, out = plain_gemm_plan(a, b)
+    want = 128 if ((m + 255) // 256) * ((n + 127) // 128) <= plan.info["grid"] // 2 else 256
+    assert plan.info["block_n"] == want and plan.info["cta_group"] == 2
+    out.fill_(float("nan"))
+    plan.run()
+    plan.run()
+    torch.cuda.synchronize()
+    _check(out, a.float() @ b.float(), k)

@@ -131,6 +131,20 @@ def test_headline_configs_resolve_as_documented():
     assert s["num_n_blocks"] == 112 and s["chunk_rows"] % 256 == 0
 
 
+def test_small_plain_problems_get_smaller_tiles():
+    """Auto tile shape, single rank: halve the tile while one wave still holds all tiles."""
+    s = _schedule(_cfg("plain", 1, 0, 1024, 1024, 1024))           # 4 x 8 = 32 pair tiles <= 74
+    assert (s["cta_group"], s["block_n"], s["tile_m"]) == (2, 128, 256)
+    s = _schedule(_cfg("plain", 1, 0, 2048, 1024, 1024))           # 8 x 8 = 64 pair tiles <= 74
+    assert (s["cta_group"], s["block_n"], s["tile_m"]) == (2, 128, 256)
+    s = _schedule(_cfg("plain", 1, 0, 4096, 1024, 1024))           # 64 full tiles fill one wave
+    assert (s["cta_group"], s["block_n"], s["tile_m"]) == (2, 256, 256)
+    s = _schedule(_cfg("plain", 1, 0, 1024, 1024, 1024, block_n=256))      # explicit shape wins
+    assert (s["cta_group"], s["block_n"]) == (2, 256)
+    s = _schedule(_cfg("ag_before", 2, 0, 1024, 1024, 1024))       # multi-rank schedules unchanged
+    assert (s["cta_group"], s["block_n"]) == (2, 256)
+
+
 @pytest.mark.parametrize("kwargs,needle", [
     (dict(mode="rs", world=3, rank=0, m=300, n=64, k=192), "multiple of"),          # rows/rank % 128
     (dict(mode="ag_before", world=2, rank=0, m=512, n=100, k=64), "multiple of"),    # n % 64 (and % 8)
