@@ -34,11 +34,18 @@ def test_tcp_rendezvous_from_torchrun_children_needs_stripped_env(tmp_path):
             q = ctx.SimpleQueue()
             p = ctx.Process(target=child, args=(rank, world, int(os.environ["MASTER_PORT"]) + 307, q))
             p.start()
-            print(f"rank {rank}:", q.get(), flush=True)
+            msg = q.get()
+            os.write(1, (f"rank {rank}: {msg}" + chr(10)).encode())       # one write: lines of two ranks never mix
             p.join()
     '''))
+    import socket
+    with socket.socket() as probe:                 # a port that is free now (and +307 most likely too)
+        probe.bind(("127.0.0.1", 0))
+        port = probe.getsockname()[1]
+    if port + 307 > 65000:
+        port -= 1000
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-           "--master-addr", "127.0.0.1", "--master-port", "29671", str(script)]
+           "--master-addr", "127.0.0.1", "--master-port", str(port), str(script)]
     proc = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
     lines = sorted(l for l in proc.stdout.splitlines() if l.startswith("rank "))
     assert lines == ["rank 0: ok", "rank 1: ok"], proc.stdout[-1500:] + proc.stderr[-1500:]
