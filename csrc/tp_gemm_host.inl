@@ -53,6 +53,7 @@ struct Resolved {
   int threads;   // 256, or 384 when the aux warps 8..11 have work (collectives, 3xTF32)
   int part0;     // first shard in visiting order
   int pairs;     // MMA pairs per cluster: 2 = four-CTA clusters with the A tile multicast
+  int wide;      // 1: a scheduled tile is two neighbouring n-blocks sharing every A stage
 };
 
 static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
@@ -124,6 +125,22 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
     const int64_t mb256 = (c.m + 255) / 256, nb128 = (c.n + 127) / 128;
     if (mb256 * nb128 <= r.grid / 2) r.block_n = 128;
   }
+  // Wide tiles (256 x 512 per CTA pair, both accumulators in TMEM at once): 25 % fewer operand
+  // bytes per MMA, but a 4-deep operand ring and an epilogue that is no longer hidden behind the
+  // next tile's main loop. 16-bit, cta_group 2, BLOCK_N 256, an even number of n-blocks.
+  // Explicit request only: measured against the 256x256 tiles it is 0.80x at k = 1024, 0.91 -
+  // 0.99x at k = 4096 .. 16384 and 1.03x only where it removes a partial wave (8192x1024x8192);
+  // sustained large GEMMs are not bound by the L2 -> SM operand stream.
+  if (c.wide_n < 0 || c.wide_n > 2) return set_error("wide_n must be 0 (auto), 1 (on) or 2 (off)");
+  {
+    const int64_t nb = (c.n + r.block_n - 1) / r.block_n;
+    const bool can = r.elem == 2 && r.cta_group == 2 && r.block_n == 256 && r.pairs == 1 && nb % 2 == 0 &&
+                     c.trace == nullptr;
+    if (c.wide_n == 1 && !can)
+      return set_error("wide_n=1 needs fp16/bf16, cta_group=2, block_n=256, one pair per cluster, no "
+                       "trace and an even number of 256-column blocks (n = %lld)", (long long)c.n);
+    r.wide = c.wide_n == 1 ? 1 : 0;
+  }
   const int cluster_ctas = r.cta_group * r.pairs;
   r.grid -= r.grid % cluster_ctas;
   if (r.grid < cluster_ctas) return set_error("no SMs to launch on");
@@ -189,12 +206,12 @@ namespace ddlb {
 static void fill_launch(cudaLaunchConfig_t& lc, cudaLaunchAttribute* attr, unsigned grid, int threads,
                         int smem_bytes, int cta_group, cudaStream_t st);
 
-template <int G, int BN, bool NM, bool F32 = false, bool SPLIT = false, int PAIRS = 1>
+template <int G, int BN, bool NM, bool F32 = false, bool SPLIT = false, int PAIRS = 1, bool WIDE = false>
 static int bind_kernel(ddlb_tp_gemm_plan* plan) {
-  using Cfg = TpGemmCfg<G, BN, SPLIT>;
-  auto k = tp_gemm_kernel<G, BN, NM, F32, SPLIT, false, PAIRS>;
+  using Cfg = TpGemmCfg<G, BN, SPLIT, WIDE>;
+  auto k = tp_gemm_kernel<G, BN, NM, F32, SPLIT, false, PAIRS, WIDE>;
   plan->kernel = reinterpret_cast<void (*)(TpGemmParams)>(k);
-  auto ke = tp_gemm_emulated_kernel<G, BN, NM, F32, SPLIT, PAIRS>;
+  auto ke = tp_gemm_emulated_kernel<G, BN, NM, F32, SPLIT, PAIRS, WIDE>;
   plan->emu_kernel = ke;
   plan->stages = Cfg::kStages;
   plan->smem_bytes = Cfg::kSmemBytes;
@@ -261,6 +278,9 @@ static int select_kernel(ddlb_tp_gemm_plan* plan) {
   }
   if (plan->res.pairs == 2)
     return nm ? bind_kernel<2, 256, true, false, false, 2>(plan) : bind_kernel<2, 256, false, false, false, 2>(plan);
+  if (plan->res.wide)
+    return nm ? bind_kernel<2, 256, true, false, false, 1, true>(plan)
+              : bind_kernel<2, 256, false, false, false, 1, true>(plan);
   if (g == 1 && bn == 256) return nm ? bind_kernel<1, 256, true>(plan) : bind_kernel<1, 256, false>(plan);
   if (g == 2 && bn == 256) return nm ? bind_kernel<2, 256, true>(plan) : bind_kernel<2, 256, false>(plan);
   if (g == 1 && bn == 128) return nm ? bind_kernel<1, 128, true>(plan) : bind_kernel<1, 128, false>(plan);
@@ -279,7 +299,7 @@ static void fill_schedule(TpGemmParams& p, const ddlb_tp_gemm_config& c, const R
   p.world = c.world;
   p.num_m_blocks = (r.a_rows + r.tile_m - 1) / r.tile_m;
   p.num_n_blocks = static_cast<int>((c.n + r.block_n - 1) / r.block_n);
-  p.sched_n_blocks = p.num_n_blocks / r.pairs;
+  p.sched_n_blocks = p.num_n_blocks / (r.pairs * (r.wide ? 2 : 1));
   p.group_m = r.group_m;
   p.part_rows = r.part_rows;
   p.out_n = static_cast<int>(c.n);
@@ -477,16 +497,20 @@ extern "C" int ddlb_tp_gemm_run(ddlb_tp_gemm_plan* plan, uint32_t epoch, void* s
   return 0;
 }
 
-extern "C" int ddlb_tp_gemm_info(const ddlb_tp_gemm_plan* plan, int32_t out[8]) {
+extern "C" int ddlb_tp_gemm_info(const ddlb_tp_gemm_plan* plan, int32_t out[12]) {
   if (plan == nullptr || out == nullptr) return ddlb::set_error("null argument");
   out[0] = plan->res.grid;
-  out[1] = plan->res.cta_group;
+  out[1] = plan->res.cta_group * plan->res.pairs;
   out[2] = plan->smem_bytes;
   out[3] = plan->res.cta_group;
   out[4] = plan->res.block_n;
   out[5] = plan->stages;
   out[6] = plan->res.threads;
   out[7] = plan->res.chunk_rows;
+  out[8] = plan->res.pairs;
+  out[9] = plan->res.wide;
+  out[10] = plan->params.pdl;
+  out[11] = 0;
   return 0;
 }
 
@@ -506,7 +530,8 @@ extern "C" int ddlb_tp_gemm_run_emulated(ddlb_tp_gemm_plan** plans, int world, u
     if (plans[r] == nullptr) return set_error("null plan %d", r);
     if (plans[r]->emu_kernel == nullptr) return set_error("traced plans cannot be emulated");
     if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group ||
-        plans[r]->res.threads != first->res.threads || plans[r]->res.pairs != first->res.pairs)
+        plans[r]->res.threads != first->res.threads || plans[r]->res.pairs != first->res.pairs ||
+        plans[r]->res.wide != first->res.wide)
       return set_error("emulated ranks must use the same kernel variant");
   }
   int dev = 0, sms = 0;
@@ -609,7 +634,8 @@ extern "C" int ddlb_tp_gemm_run_emulated_static(ddlb_tp_gemm_plan** plans, int w
     if (plans[r] == nullptr) return set_error("null plan %d", r);
     if (plans[r]->emu_kernel == nullptr) return set_error("traced plans cannot be emulated");
     if (plans[r]->emu_kernel != first->emu_kernel || plans[r]->res.cta_group != first->res.cta_group ||
-        plans[r]->res.threads != first->res.threads || plans[r]->res.pairs != first->res.pairs)
+        plans[r]->res.threads != first->res.threads || plans[r]->res.pairs != first->res.pairs ||
+        plans[r]->res.wide != first->res.wide)
       return set_error("emulated ranks must use the same kernel variant");
   }
   int dev = 0, sms = 0;

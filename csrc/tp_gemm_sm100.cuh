@@ -110,13 +110,18 @@ struct TpGemmParams {
   uint8_t* out_raw[kMaxWorld];
 };
 
-template <int kCtaGroup, int kBlockN, bool kSplit = false>
+// kWide: one scheduled tile = TWO neighbouring n-blocks (256 x 2*BLOCK_N per CTA pair) that share
+// every A stage; both accumulators live in TMEM at once (no double buffering, the epilogue is
+// exposed once per tile), and a k-block moves 48 KB instead of 2 x 32 KB per CTA.
+template <int kCtaGroup, int kBlockN, bool kSplit = false, bool kWide = false>
 struct TpGemmCfg {
+  static_assert(!kWide || (kCtaGroup == 2 && kBlockN == 256 && !kSplit), "wide tiles: cta_group 2, BLOCK_N 256");
+  static constexpr int kNSub = kWide ? 2 : 1;                    // n-blocks per scheduled tile
   static constexpr int kTileM = kBlockM * kCtaGroup;
   static constexpr int kLoadN = kBlockN / kCtaGroup;            // B columns staged per CTA
   static constexpr int kStageA = kBlockM * kBlockK * 2;
   static constexpr int kStageB = kLoadN * kBlockK * 2;
-  static constexpr int kStageOps = kStageA + kStageB;
+  static constexpr int kStageOps = kStageA + kNSub * kStageB;
   // 3xTF32: every stage also holds the low-order parts of A and B
   static constexpr int kStageBytes = kSplit ? 2 * kStageOps : kStageOps;
   static constexpr int kStagesRaw = kSmemBudget / kStageBytes;
@@ -615,10 +620,12 @@ __device__ __forceinline__ void rs_reduce_loop(const TpGemmParams& p, int lane, 
 // with one pair per cluster the operand stream from L2 runs at the fabric's cap (~6.6 KB/clk,
 // 1.07 GB per 100 us launch) and the tensor pipe idles 22 % of its active cycles.
 template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kSplit = false,
-          bool kTrace = false, int kPairs = 1>
+          bool kTrace = false, int kPairs = 1, bool kWide = false>
 __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cluster,
                                              const int nclusters) {
-  using Cfg = TpGemmCfg<kCtaGroup, kBlockN, kSplit>;
+  using Cfg = TpGemmCfg<kCtaGroup, kBlockN, kSplit, kWide>;
+  constexpr int kNSub = Cfg::kNSub;
+  static_assert(!kWide || (kPairs == 1 && !kF32), "wide tiles: one pair per cluster, 16-bit operands");
   static_assert(!kSplit || kF32, "the hi/lo split exists for fp32 only");
   static_assert(kPairs == 1 || (kPairs == 2 && kCtaGroup == 2 && !kSplit), "two pairs need cta_group 2");
   constexpr int kClusterCtas = kCtaGroup * kPairs;
@@ -710,7 +717,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         tr.ev(kEvFlagWaited, static_cast<uint32_t>(t));
       }
       const int m0 = tc.m_blk * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
-      const int n0 = (tc.n_blk * kPairs + static_cast<int>(pair)) * kBlockN +
+      const int n0 = (tc.n_blk * kPairs + static_cast<int>(pair)) * kNSub * kBlockN +
                      static_cast<int>(cta_rank) * Cfg::kLoadN;
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
         mbar_wait(bar_empty + stage * 8, phase ^ 1u);
@@ -732,10 +739,13 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
         } else {
           tma_load_2d<kCtaGroup>(smem_u32(sa), &p.tmA, fb, kb * kKPerStage, m0);
         }
-        if constexpr (kBNMajor)
-          tma_load_3d<kCtaGroup>(smem_u32(sb), &p.tmB, fb, 0, kb * kKPerStage, n0 / kRowElems);
-        else
-          tma_load_2d<kCtaGroup>(smem_u32(sb), &p.tmB, fb, kb * kKPerStage, n0);
+#pragma unroll
+        for (int sub = 0; sub < kNSub; ++sub) {
+          const int ns = n0 + sub * kBlockN;
+          const uint32_t sbs = smem_u32(sb) + sub * Cfg::kStageB;
+          if constexpr (kBNMajor) tma_load_3d<kCtaGroup>(sbs, &p.tmB, fb, 0, kb * kKPerStage, ns / kRowElems);
+          else tma_load_2d<kCtaGroup>(sbs, &p.tmB, fb, kb * kKPerStage, ns);
+        }
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
       }
     }
@@ -753,6 +763,7 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
     Tracer<kTrace> tr(p, cta, 1);
     for (int t = cluster; t < num_tiles; t += nclusters) {
       mbar_wait(bar_tempty + acc * 8, acc_phase ^ 1u);
+      if constexpr (kWide) mbar_wait(bar_tempty + 8, acc_phase ^ 1u);    // both accumulators drained
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * kBlockN);
       for (int kb = 0; kb < p.num_k_blocks; ++kb) {
@@ -775,6 +786,9 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
             }
           } else {
             umma_f16<kCtaGroup>(tmem_d, ak, bk, p.idesc, static_cast<uint32_t>((kb | k) != 0));
+            if constexpr (kWide)          // second n-block: same A, next B tile, next accumulator
+              umma_f16<kCtaGroup>(tmem_d + kBlockN, ak, bk + static_cast<uint64_t>(Cfg::kStageB >> 4),
+                                  p.idesc, static_cast<uint32_t>((kb | k) != 0));
           }
         }
         // smem slot reusable when the MMAs retire: every CTA of the cluster hears it (with two
@@ -784,8 +798,11 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
       }
       umma_commit<kCtaGroup>(bar_tfull + acc * 8,          // accumulator ready: this pair's epilogues
                              static_cast<uint16_t>(0x3u << leader_rank));
+      if constexpr (kWide)
+        umma_commit<kCtaGroup>(bar_tfull + 8, static_cast<uint16_t>(0x3u << leader_rank));
       tr.ev(kEvTileIssued, static_cast<uint32_t>(t));
-      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      if constexpr (kWide) acc_phase ^= 1u;                  // acc stays 0: both slots used per tile
+      else if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
   } else if (kSplit && warp >= 8) {
     // -------------------------------------------------------- 3xTF32 split warps
@@ -869,127 +886,131 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
       const TileCoord tc = tile_coord(p, t);
       const int row_cta = tc.m_blk * Cfg::kTileM + static_cast<int>(cta_rank) * kBlockM;
       const int row0 = row_cta + q * 32;
-      const int n_blk = tc.n_blk * kPairs + static_cast<int>(pair);
-      const int n0 = n_blk * kBlockN;
-      mbar_wait(bar_tfull + acc * 8, acc_phase);
-      tc_fence_after();
-      tr.ev(kEvAccReady, static_cast<uint32_t>(t));
+      // wide tiles: the two n-blocks of the tile are drained one after the other (accumulator 0, 1)
+#pragma unroll 1
+      for (int sub = 0; sub < kNSub; ++sub) {
+        const int n_blk = (tc.n_blk * kPairs + static_cast<int>(pair)) * kNSub + sub;
+        const int n0 = n_blk * kBlockN;
+        mbar_wait(bar_tfull + acc * 8, acc_phase);
+        tc_fence_after();
+        tr.ev(kEvAccReady, static_cast<uint32_t>(t));
 
-      int out_row = row0;
-      int cta_tile = 0;
-      uint8_t* rs_dst = nullptr;
-      if (p.mode == kModeRS) {
-        // row inside the owner's shard; staging slot [parity][src] at the owner (push) or
-        // [parity][owner] locally (pull)
-        out_row = row0 - tc.part * p.part_rows;
-        cta_tile = ((row_cta - tc.part * p.part_rows) / kBlockM) * p.num_n_blocks + n_blk;
-        const size_t slot_bytes = static_cast<size_t>(p.rs_tiles) * (4 * (kBlockN / kRowElems)) * kEpiBufBytes;
-        rs_dst = p.rs_transport == kRsPush
-                     ? p.stage_base[tc.part] + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes
-                     : p.stage_base[p.rank] + (static_cast<size_t>(parity) * p.world + tc.part) * slot_bytes;
-      } else if (p.mode == kModeAGAfter) {
-        out_row = p.rank * p.part_rows + row0;
-      }
+        int out_row = row0;
+        int cta_tile = 0;
+        uint8_t* rs_dst = nullptr;
+        if (p.mode == kModeRS) {
+          // row inside the owner's shard; staging slot [parity][src] at the owner (push) or
+          // [parity][owner] locally (pull)
+          out_row = row0 - tc.part * p.part_rows;
+          cta_tile = ((row_cta - tc.part * p.part_rows) / kBlockM) * p.num_n_blocks + n_blk;
+          const size_t slot_bytes = static_cast<size_t>(p.rs_tiles) * (4 * (kBlockN / kRowElems)) * kEpiBufBytes;
+          rs_dst = p.rs_transport == kRsPush
+                       ? p.stage_base[tc.part] + (static_cast<size_t>(parity) * p.world + p.rank) * slot_bytes
+                       : p.stage_base[p.rank] + (static_cast<size_t>(parity) * p.world + tc.part) * slot_bytes;
+        } else if (p.mode == kModeAGAfter) {
+          out_row = p.rank * p.part_rows + row0;
+        }
 
 #pragma unroll 1
-      for (int c = 0; c < kBlockN / kRowElems; ++c) {
-        // 32 rows x 128 bytes of output per step: this lane's row, as 32 words
-        uint32_t packed[32];
-        if constexpr (kF32) {
-          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
-                                 static_cast<uint32_t>(acc * kBlockN + c * 32);
-          tmem_ld_32x32b_x32(taddr, &packed[0]);
-          tmem_ld_wait();
-          if (p.act != kActNone) {
+        for (int c = 0; c < kBlockN / kRowElems; ++c) {
+          // 32 rows x 128 bytes of output per step: this lane's row, as 32 words
+          uint32_t packed[32];
+          if constexpr (kF32) {
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                                   static_cast<uint32_t>(acc * kBlockN + c * 32);
+            tmem_ld_32x32b_x32(taddr, &packed[0]);
+            tmem_ld_wait();
+            if (p.act != kActNone) {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                packed[i] = __float_as_uint(apply_act(__uint_as_float(packed[i]), p.act));
+            }
+          } else {
+            uint32_t v[64];
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                                   static_cast<uint32_t>(acc * kBlockN + c * 64);
+            tmem_ld_32x32b_x32(taddr, &v[0]);
+            tmem_ld_32x32b_x32(taddr + 32, &v[32]);
+            tmem_ld_wait();
+            if (p.act != kActNone) {
+#pragma unroll
+              for (int i = 0; i < 64; ++i) v[i] = __float_as_uint(apply_act(__uint_as_float(v[i]), p.act));
+            }
 #pragma unroll
             for (int i = 0; i < 32; ++i)
-              packed[i] = __float_as_uint(apply_act(__uint_as_float(packed[i]), p.act));
+              packed[i] = pack2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]), bf16);
           }
-        } else {
-          uint32_t v[64];
-          const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
-                                 static_cast<uint32_t>(acc * kBlockN + c * 64);
-          tmem_ld_32x32b_x32(taddr, &v[0]);
-          tmem_ld_32x32b_x32(taddr + 32, &v[32]);
-          tmem_ld_wait();
-          if (p.act != kActNone) {
-#pragma unroll
-            for (int i = 0; i < 64; ++i) v[i] = __float_as_uint(apply_act(__uint_as_float(v[i]), p.act));
-          }
-#pragma unroll
-          for (int i = 0; i < 32; ++i)
-            packed[i] = pack2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]), bf16);
-        }
 
-        if (lane == 0) bulk_wait_read<1>();     // the TMA store that last used this buffer has read it
-        __syncwarp();
-        const uint32_t sbase = smem_u32(ebuf + buf * kEpiBufBytes);
-        const uint32_t srow = sbase + lane * 128;
+          if (lane == 0) bulk_wait_read<1>();     // the TMA store that last used this buffer has read it
+          __syncwarp();
+          const uint32_t sbase = smem_u32(ebuf + buf * kEpiBufBytes);
+          const uint32_t srow = sbase + lane * 128;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const uint32_t dst = srow + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(packed[4 * j]),
-                       "r"(packed[4 * j + 1]), "r"(packed[4 * j + 2]), "r"(packed[4 * j + 3])
-                       : "memory");
-        }
-        const int col0 = n0 + c * kRowElems;
-        const int colb = col0 * kElem;
-        if (p.mode == kModeRS) {
-          __syncwarp();
-          // unit-major staging: this chunk is unit (cta_tile, q, c), 4 KiB contiguous
-          store_chunk_st128<false>(rs_dst + (static_cast<size_t>(cta_tile * 4 + q) * (kBlockN / kRowElems) + c) *
-                                                kEpiBufBytes,
-                                   128, 0, 0, 128, sbase, lane);
-          __syncwarp();            // every lane has read the staged rows before they are reused
-        } else if (p.mode == kModeAGAfter && p.epi_transport == kEpiMulticast) {
-          __syncwarp();
-          store_chunk_st128<true>(p.mc_ptr, pitch, out_row, colb, static_cast<int>(pitch), sbase, lane);
-          __syncwarp();
-        } else if (p.mode == kModeAGAfter && p.epi_transport == kEpiSt128) {
-          fence_proxy_async_smem();
-          __syncwarp();
-          for (int d = 0; d < p.world; ++d)
-            if (d != p.rank)
-              store_chunk_st128<false>(p.out_raw[d], pitch, out_row, colb, static_cast<int>(pitch), sbase, lane);
-          if (lane == 0) {
-            tma_store_2d(&p.tmOut[p.rank], sbase, col0, out_row);
-            bulk_commit();
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t dst = srow + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(packed[4 * j]),
+                         "r"(packed[4 * j + 1]), "r"(packed[4 * j + 2]), "r"(packed[4 * j + 3])
+                         : "memory");
           }
-          __syncwarp();
-        } else {
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) {
-            if (p.mode == kModeAGAfter) {
-              for (int d = 0; d < p.world; ++d) tma_store_2d(&p.tmOut[d], sbase, col0, out_row);
-            } else {
+          const int col0 = n0 + c * kRowElems;
+          const int colb = col0 * kElem;
+          if (p.mode == kModeRS) {
+            __syncwarp();
+            // unit-major staging: this chunk is unit (cta_tile, q, c), 4 KiB contiguous
+            store_chunk_st128<false>(rs_dst + (static_cast<size_t>(cta_tile * 4 + q) * (kBlockN / kRowElems) + c) *
+                                                  kEpiBufBytes,
+                                     128, 0, 0, 128, sbase, lane);
+            __syncwarp();            // every lane has read the staged rows before they are reused
+          } else if (p.mode == kModeAGAfter && p.epi_transport == kEpiMulticast) {
+            __syncwarp();
+            store_chunk_st128<true>(p.mc_ptr, pitch, out_row, colb, static_cast<int>(pitch), sbase, lane);
+            __syncwarp();
+          } else if (p.mode == kModeAGAfter && p.epi_transport == kEpiSt128) {
+            fence_proxy_async_smem();
+            __syncwarp();
+            for (int d = 0; d < p.world; ++d)
+              if (d != p.rank)
+                store_chunk_st128<false>(p.out_raw[d], pitch, out_row, colb, static_cast<int>(pitch), sbase, lane);
+            if (lane == 0) {
               tma_store_2d(&p.tmOut[p.rank], sbase, col0, out_row);
+              bulk_commit();
             }
-            bulk_commit();
+            __syncwarp();
+          } else {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              if (p.mode == kModeAGAfter) {
+                for (int d = 0; d < p.world; ++d) tma_store_2d(&p.tmOut[d], sbase, col0, out_row);
+              } else {
+                tma_store_2d(&p.tmOut[p.rank], sbase, col0, out_row);
+              }
+              bulk_commit();
+            }
           }
+          buf ^= 1;
         }
-        buf ^= 1;
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if (kCtaGroup == 2 && cta_rank != 0) mbar_arrive_cluster(tempty_leader + acc * 8);
-        else mbar_arrive(bar_tempty + acc * 8);
-      }
-      tr.ev(kEvTileStored, static_cast<uint32_t>(t));
-      if (p.mode == kModeRS) {
-        // announce the tile to its owner as soon as this warp's stores have been performed
-        // (the accumulator is already released, only this warp waits for the round trip)
-        // push to a peer: the stores crossed NVLink, only a system-scope fence knows when they
-        // have landed. Stores into LOCAL staging (own tiles; every tile of the pull transports)
-        // are complete for every reader, local or remote, once they are in this GPU's L2: a
-        // GPU-scope fence (~1 us instead of ~5 us).
-        if (p.rs_transport == kRsPush && tc.part != p.rank) __threadfence_system();
-        else __threadfence();
+        tc_fence_before();
         __syncwarp();
-        if (lane == 0) red_add_relaxed_sys(p.sig_peer[tc.part] + kSigChunk + cta_tile, 1u);
+        if (lane == 0) {
+          if (kCtaGroup == 2 && cta_rank != 0) mbar_arrive_cluster(tempty_leader + acc * 8);
+          else mbar_arrive(bar_tempty + acc * 8);
+        }
+        tr.ev(kEvTileStored, static_cast<uint32_t>(t));
+        if (p.mode == kModeRS) {
+          // announce the tile to its owner as soon as this warp's stores have been performed
+          // (the accumulator is already released, only this warp waits for the round trip)
+          // push to a peer: the stores crossed NVLink, only a system-scope fence knows when they
+          // have landed. Stores into LOCAL staging (own tiles; every tile of the pull transports)
+          // are complete for every reader, local or remote, once they are in this GPU's L2: a
+          // GPU-scope fence (~1 us instead of ~5 us).
+          if (p.rs_transport == kRsPush && tc.part != p.rank) __threadfence_system();
+          else __threadfence();
+          __syncwarp();
+          if (lane == 0) red_add_relaxed_sys(p.sig_peer[tc.part] + kSigChunk + cta_tile, 1u);
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
-      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
     if (lane == 0) bulk_wait<0>();
     tr.ev(kEvEnd, 0);
@@ -1020,13 +1041,13 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
 
 // One rank per process / GPU: parameters in the kernel parameter space.
 template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kSplit = false,
-          bool kTrace = false, int kPairs = 1>
+          bool kTrace = false, int kPairs = 1, bool kWide = false>
 __global__ void __launch_bounds__(kMaxThreads, 1)
 tp_gemm_kernel(const __grid_constant__ TpGemmParams p) {
   constexpr bool kClustered = kCtaGroup * kPairs > 1;
   const int cluster = kClustered ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
   const int nclusters = kClustered ? static_cast<int>(num_clusters_x()) : static_cast<int>(gridDim.x);
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kSplit, kTrace, kPairs>(p, cluster, nclusters);
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kSplit, kTrace, kPairs, kWide>(p, cluster, nclusters);
 }
 
 // Several ranks emulated by ONE launch on one GPU (tests): the grid is split into
@@ -1034,13 +1055,13 @@ tp_gemm_kernel(const __grid_constant__ TpGemmParams p) {
 // CTAs of one launch are co-resident (grid <= SM count), so ranks that wait on
 // each other make progress, which separate launches on one GPU cannot guarantee.
 template <int kCtaGroup, int kBlockN, bool kBNMajor, bool kF32 = false, bool kSplit = false,
-          int kPairs = 1>
+          int kPairs = 1, bool kWide = false>
 __global__ void __launch_bounds__(kMaxThreads, 1)
 tp_gemm_emulated_kernel(const TpGemmParams* __restrict__ plist, int clusters_per_rank) {
   constexpr bool kClustered = kCtaGroup * kPairs > 1;
   const int cluster = kClustered ? static_cast<int>(cluster_id_x()) : static_cast<int>(blockIdx.x);
   const int vr = cluster / clusters_per_rank;
-  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kSplit, false, kPairs>(
+  tp_gemm_body<kCtaGroup, kBlockN, kBNMajor, kF32, kSplit, false, kPairs, kWide>(
       plist[vr], cluster - vr * clusters_per_rank, clusters_per_rank);
 }
 

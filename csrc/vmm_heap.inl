@@ -1,6 +1,6 @@
 // Symmetric heap on the CUDA virtual-memory API with an NVLS multicast object.
-// Included by ddlb_b200.cu. EXPERIMENTAL: written after round 1's GPU budget was spent; it
-// has compiled but never run. The production heap is the cudaIpc one in runtime.inl.
+// Included by ddlb_b200.cu. The default heap on NVSwitch systems (2, 4 and 8 GPUs:
+// tests/test_vmm_multigpu.py); the cudaIpc heap in runtime.inl is the fallback.
 //
 // Every rank creates one physical allocation (cuMemCreate, shareable as a POSIX file
 // descriptor), maps all ranks' allocations into one reserved VA range (rank r at

@@ -41,7 +41,7 @@ class TpGemmConfig(Structure):
         ("rank", c_int32), ("world", c_int32), ("chunk_rows", c_int32),
         ("ag_transport", c_int32), ("epi_transport", c_int32), ("rs_transport", c_int32),
         ("unrotated", c_int32), ("fp32_mode", c_int32), ("epilogue_act", c_int32),
-        ("comm_warps", c_int32), ("cluster_pairs", c_int32), ("pdl", c_int32),
+        ("comm_warps", c_int32), ("cluster_pairs", c_int32), ("pdl", c_int32), ("wide_n", c_int32),
         ("m", c_int64), ("n", c_int64), ("k", c_int64),
         ("a", c_void_p), ("b", c_void_p),
         ("out", c_void_p * MAX_WORLD), ("peer_a", c_void_p * MAX_WORLD),
@@ -93,7 +93,7 @@ def lib() -> ctypes.CDLL:
     L.ddlb_tp_gemm_sig_words.restype = c_int64
     L.ddlb_tp_gemm_create.argtypes = [POINTER(TpGemmConfig), POINTER(c_void_p)]
     L.ddlb_tp_gemm_run.argtypes = [c_void_p, c_uint32, c_void_p]
-    L.ddlb_tp_gemm_info.argtypes = [c_void_p, POINTER(c_int32 * 8)]
+    L.ddlb_tp_gemm_info.argtypes = [c_void_p, POINTER(c_int32 * 12)]
     L.ddlb_tp_gemm_destroy.argtypes = [c_void_p]
     L.ddlb_tp_gemm_run_emulated.argtypes = [POINTER(c_void_p), c_int, c_uint32, c_void_p]
     L.ddlb_tp_gemm_run_emulated_static.argtypes = [POINTER(c_void_p), c_int, c_uint32, c_void_p]

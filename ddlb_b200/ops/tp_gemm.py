@@ -56,11 +56,11 @@ class TpGemmPlan:
         N.check(self._lib.ddlb_tp_gemm_create(ctypes.byref(cfg), ctypes.byref(handle)),
                 "tp_gemm_create")
         self._h = handle
-        info = (ctypes.c_int32 * 8)()
+        info = (ctypes.c_int32 * 12)()
         N.check(self._lib.ddlb_tp_gemm_info(self._h, ctypes.byref(info)), "tp_gemm_info")
         self.info: Dict[str, int] = dict(zip(
             ("grid", "cluster", "smem_bytes", "cta_group", "block_n", "stages", "threads",
-             "chunk_rows"), list(info)))
+             "chunk_rows", "pairs", "wide", "pdl"), list(info)))
         self.epoch = 0
         self.launches = 0
 
@@ -88,7 +88,8 @@ def _base_config(mode: int, dtype, m: int, n: int, k: int, rank: int, world: int
                  b_layout: int, cta_group: int, block_n: int, group_m: int, num_sms: int,
                  chunk_rows: int = 0, fp32_mode: str = "3xtf32",
                  unrotated: bool = False, activation: Optional[str] = None,
-                 cluster_pairs: int = 0, pdl: Optional[bool] = None) -> N.TpGemmConfig:
+                 cluster_pairs: int = 0, pdl: Optional[bool] = None,
+                 wide_n: Optional[bool] = None) -> N.TpGemmConfig:
     if fp32_mode not in FP32_MODES:
         raise ValueError(f"fp32_mode must be one of {sorted(FP32_MODES)}, got {fp32_mode!r}")
     if activation not in ACTIVATIONS:
@@ -102,6 +103,7 @@ def _base_config(mode: int, dtype, m: int, n: int, k: int, rank: int, world: int
     cfg.epilogue_act = ACTIVATIONS[activation]
     cfg.cluster_pairs = int(cluster_pairs)
     cfg.pdl = 0 if pdl is None else (1 if pdl else 2)   # None: on for single-rank plans
+    cfg.wide_n = 0 if wide_n is None else (1 if wide_n else 2)   # opt-in: auto never picks it
     cfg.m, cfg.n, cfg.k = m, n, k
     return cfg
 
@@ -109,7 +111,8 @@ def _base_config(mode: int, dtype, m: int, n: int, k: int, rank: int, world: int
 def plain_gemm_plan(a, b, out=None, *, b_is_nk: bool = False, cta_group: int = 0,
                     block_n: int = 0, group_m: int = 0, num_sms: int = 0,
                     fp32_mode: str = "3xtf32", activation: Optional[str] = None,
-                    cluster_pairs: int = 0, pdl: Optional[bool] = None):
+                    cluster_pairs: int = 0, pdl: Optional[bool] = None,
+                    wide_n: Optional[bool] = None):
     """Plan for ``out[m,n] = a[m,k] @ b`` with ``b`` ``[k,n]`` (or ``[n,k]`` if ``b_is_nk``).
 
     ``pdl`` (default on): the launch uses programmatic stream serialization, so the kernel's
@@ -126,7 +129,7 @@ def plain_gemm_plan(a, b, out=None, *, b_is_nk: bool = False, cta_group: int = 0
     b, b_is_nk = _weight_for_kernel(b, b_is_nk)
     cfg = _base_config(N.MODE_PLAIN, a.dtype, m, n, k, 0, 1, N.B_NK if b_is_nk else N.B_KN,
                        cta_group, block_n, group_m, num_sms, fp32_mode=fp32_mode,
-                       activation=activation, cluster_pairs=cluster_pairs, pdl=pdl)
+                       activation=activation, cluster_pairs=cluster_pairs, pdl=pdl, wide_n=wide_n)
     cfg.a, cfg.b = a.data_ptr(), b.data_ptr()
     cfg.out[0] = out.data_ptr()
     return TpGemmPlan(cfg, keepalive=(a, b, out)), out
@@ -200,7 +203,7 @@ class FusedAllGatherGemm(_FusedBase):
                  b_is_nk: bool = False, transport: str = "auto", trace: bool = False,
                  fp32_mode: str = "3xtf32", unrotated: bool = False,
                  activation: Optional[str] = None, out=None, comm_warps: int = 0,
-                 cluster_pairs: int = 0):
+                 cluster_pairs: int = 0, wide_n: Optional[bool] = None):
         super().__init__(heap, rank, world)
         import torch
         if m % world:
@@ -210,7 +213,7 @@ class FusedAllGatherGemm(_FusedBase):
         b, b_is_nk = _weight_for_kernel(b, b_is_nk)
         layout = N.B_NK if b_is_nk else N.B_KN
         common = dict(fp32_mode=fp32_mode, unrotated=unrotated, activation=activation,
-                      cluster_pairs=cluster_pairs)
+                      cluster_pairs=cluster_pairs, wide_n=wide_n)
         if out is not None and order != "AG_before":
             raise ValueError("a caller-provided output is supported for order='AG_before' only")
         if order == "AG_before":
@@ -324,7 +327,7 @@ class FusedGemmReduceScatter(_FusedBase):
                  chunk_rows: int = 0, cta_group: int = 0, block_n: int = 0, group_m: int = 0,
                  num_sms: int = 0, b_is_nk: bool = False, trace: bool = False,
                  transport: str = "auto", fp32_mode: str = "3xtf32", unrotated: bool = False,
-                 cluster_pairs: int = 0):
+                 cluster_pairs: int = 0, wide_n: Optional[bool] = None):
         super().__init__(heap, rank, world)
         import torch
         self.trace_buf = None
@@ -345,7 +348,8 @@ class FusedGemmReduceScatter(_FusedBase):
         self.transport = _resolve_transport(transport, RS_TRANSPORTS, default, heap, "tp_rowwise")
         if world == 1:
             cfg = _base_config(N.MODE_PLAIN, dtype, m, n, k, 0, 1, layout, cta_group, block_n,
-                               group_m, num_sms, fp32_mode=fp32_mode, cluster_pairs=cluster_pairs)
+                               group_m, num_sms, fp32_mode=fp32_mode, cluster_pairs=cluster_pairs,
+                               wide_n=wide_n)
             cfg.out[0] = self.out.data_ptr()
         else:
             # staging is unit-major and covers whole 256-column blocks (see rs_reduce_loop)
@@ -353,7 +357,7 @@ class FusedGemmReduceScatter(_FusedBase):
             st_off, self.staging = heap.empty((2, world, rows, n_pad), dtype)
             cfg = _base_config(N.MODE_RS, dtype, m, n, k, rank, world, layout, cta_group, block_n,
                                group_m, num_sms, chunk_rows, fp32_mode=fp32_mode,
-                               unrotated=unrotated, cluster_pairs=cluster_pairs)
+                               unrotated=unrotated, cluster_pairs=cluster_pairs, wide_n=wide_n)
             cfg.rs_transport = RS_TRANSPORTS[self.transport]
             for p in range(world):
                 cfg.stage[p] = heap.ptr(st_off, p)

@@ -51,10 +51,11 @@ int ddlb_symm_barrier(ddlb_symm* s, void* stream);
  * = 1, 2, 3, ... per call, identical on all ranks */
 int ddlb_barrier_raw(void* const* pad_bases, int rank, int world, uint32_t epoch, void* stream);
 
-/* ------------------------------------------- VMM heap + NVLS multicast (EXPERIMENTAL)
+/* ------------------------------------------- VMM heap + NVLS multicast
  * Same role as ddlb_symm_* but on cuMemCreate/cuMemMap with POSIX file-descriptor handles and,
  * where the devices support it, a multicast object (multimem.st / multimem.ld_reduce through
- * the NVSwitch). Written after round 1's GPU budget was spent: compiled, never run. Protocol:
+ * the NVSwitch). The default heap of the Python layer on NVSwitch systems (runs at 2, 4 and 8
+ * GPUs, tests/test_vmm_multigpu.py). Protocol:
  *   every rank: ddlb_vmm_create; ddlb_vmm_export_fd -> send fd to peers; ddlb_vmm_import_peer
  *   rank 0: ddlb_vmm_mc_create -> send fd; others: ddlb_vmm_mc_import
  *   every rank: ddlb_vmm_mc_add_device; HOST BARRIER; ddlb_vmm_mc_bind
@@ -136,7 +137,12 @@ typedef struct ddlb_tp_gemm_config {
                           * every global access still waits for that kernel (griddepcontrol.wait).
                           * 0 = auto (on when world == 1), 1 = on, 2 = off; DDLB_PDL=0 in the
                           * environment turns it off everywhere. No reference counterpart. */
-  int64_t m, n, k;      /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
+  int32_t wide_n;        /* wide tiles: a CTA pair computes 256 x 512 (two neighbouring n-blocks share
+                          * every A stage, both accumulators fill TMEM): 25 % fewer operand bytes per
+                          * MMA, epilogue not overlapped. fp16/bf16, cta_group 2, block_n 256, even
+                          * number of n-blocks. 1 = on; 0 (auto) and 2 = off: measured 0.80 - 1.03x of
+                          * the 256 x 256 tiles, so auto never picks it. No reference counterpart. */
+  int64_t m, n, k;       /* GLOBAL problem C[m,n] = A[m,k] B[k,n] of the primitive */
   /* PLAIN:     a = A[m,k]                 out[rank] = C[m,n]
    * AG_BEFORE: a = gathered A[m,k] (own shard rows already in place), peer_a[r] = rank r's
    *            gathered buffer, out[rank] = C[m,n]; mc_ptr = multicast alias of the gathered A
@@ -166,9 +172,9 @@ int64_t ddlb_tp_gemm_sig_words(const ddlb_tp_gemm_config* cfg);
 int ddlb_tp_gemm_create(const ddlb_tp_gemm_config* cfg, ddlb_tp_gemm_plan** out);
 /* epoch: 1, 2, 3, ... incremented by the caller on every launch, identical on all ranks */
 int ddlb_tp_gemm_run(ddlb_tp_gemm_plan* plan, uint32_t epoch, void* stream);
-/* resolved launch shape: {grid, cluster, smem_bytes, cta_group, block_n, stages, threads,
- * chunk_rows}; */
-int ddlb_tp_gemm_info(const ddlb_tp_gemm_plan* plan, int32_t out[8]);
+/* resolved launch shape: {grid, CTAs per cluster, smem_bytes, cta_group, block_n, stages, threads,
+ * chunk_rows, pairs per cluster, wide tiles (0/1), programmatic dependent launch (0/1), 0} */
+int ddlb_tp_gemm_info(const ddlb_tp_gemm_plan* plan, int32_t out[12]);
 int ddlb_tp_gemm_destroy(ddlb_tp_gemm_plan* plan);
 /* Tests on one GPU: run `world` plans (one per emulated rank, all created on the current
  * device, same kernel variant) as ONE launch whose CTAs are split between the ranks, so

@@ -137,8 +137,10 @@ def test_reduce_scatter_n_not_multiple_of_block_n(n):
 
 
 @pytest.mark.parametrize("world", [2, 4])
-def test_two_pair_clusters_fused_emulated(world):
-    """Every fused mode on clusters of four CTAs (A multicast across two MMA pairs)."""
+@pytest.mark.parametrize("variant", [dict(cluster_pairs=2), dict(wide_n=True)], ids=["two_pair", "wide"])
+def test_tile_variants_fused_emulated(world, variant):
+    """Every fused mode on clusters of four CTAs (A multicast across two MMA pairs) and on wide
+    tiles (two n-blocks per CTA pair sharing every A stage)."""
     import torch
     from ddlb_b200.ops.emulation import make_emulated_heaps, run_emulated
     from ddlb_b200.ops.tp_gemm import FusedAllGatherGemm, FusedGemmReduceScatter
@@ -148,7 +150,7 @@ def test_two_pair_clusters_fused_emulated(world):
     heaps = make_emulated_heaps(world, 8 * m * max(k, 2 * n) * 2 + (8 << 20))
     for order, transport in (("AG_before", "pull"), ("AG_before", "push"), ("AG_after", "tma")):
         ops = [FusedAllGatherGemm(heaps[r], r, world, m, n, k, a.dtype, b, order=order, transport=transport,
-                                  cluster_pairs=2) for r in range(world)]
+                                  **variant) for r in range(world)]
         for r, op in enumerate(ops):
             op.a_shard.copy_(a[r * rows:(r + 1) * rows])
         torch.cuda.synchronize()
@@ -159,14 +161,14 @@ def test_two_pair_clusters_fused_emulated(world):
             run_emulated([op.plans[idx] for op in ops], epoch)
             torch.cuda.synchronize()
             for r, op in enumerate(ops):
-                _tol_check(op.out[idx], ref, k, f"{order}/{transport} pairs=2 rank {r} epoch {epoch}")
+                _tol_check(op.out[idx], ref, k, f"{order}/{transport} {variant} rank {r} epoch {epoch}")
         for op in ops:
             op.close()
     for transport in ("push", "pull"):
         ops = [FusedGemmReduceScatter(heaps[r], r, world, m, n, k, a.dtype,
                                       a[:, r * kk:(r + 1) * kk].contiguous(),
                                       b[r * kk:(r + 1) * kk].contiguous(), transport=transport,
-                                      cluster_pairs=2) for r in range(world)]
+                                      **variant) for r in range(world)]
         for epoch in (1, 2, 3):
             for op in ops:
                 op.out.fill_(float("nan"))
@@ -175,7 +177,7 @@ def test_two_pair_clusters_fused_emulated(world):
             run_emulated([op.plan for op in ops], epoch)
             torch.cuda.synchronize()
             for r, op in enumerate(ops):
-                _tol_check(op.out, ref[r * rows:(r + 1) * rows], k, f"RS/{transport} pairs=2 rank {r} epoch {epoch}")
+                _tol_check(op.out, ref[r * rows:(r + 1) * rows], k, f"RS/{transport} {variant} rank {r} epoch {epoch}")
         for op in ops:
             op.close()
     for h in heaps:

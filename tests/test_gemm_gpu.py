@@ -142,3 +142,26 @@ def test_auto_tile_shape(shape):
     plan.run()
     torch.cuda.synchronize()
     _check(out, a.float() @ b.float(), k)
+
+
+@pytest.mark.parametrize("b_is_nk", [False, True])
+@pytest.mark.parametrize("shape", [(512, 512, 256), (384, 960, 200), (1024, 1536, 1024), (2048, 1024, 4096)])
+def test_wide_tiles(shape, b_is_nk):
+    """256 x 512 tiles per CTA pair: two accumulators share every A stage (explicit request only)."""
+    import torch
+    from ddlb_b200.ops.tp_gemm import plain_gemm_plan
+    torch.manual_seed(5)
+    m, n, k = shape
+    a = torch.randn(m, k, device="cuda").bfloat16()
+    b_kn = torch.randn(k, n, device="cuda").bfloat16()
+    b = b_kn.t().contiguous() if b_is_nk else b_kn
+    plan, out = plain_gemm_plan(a, b, b_is_nk=b_is_nk, cta_group=2, block_n=256,
+                                wide_n=True)
+    assert plan.info["wide"] == 1 and plan.info["stages"] == 4
+    out.fill_(float("nan"))
+    for _ in range(3):
+        plan.run()
+    torch.cuda.synchronize()
+    _check(out, a.float() @ b_kn.float(), k)
+    with pytest.raises(Exception, match="wide_n"):
+        plain_gemm_plan(a[:, :64].contiguous(), b_kn[:64, :768].contiguous(), wide_n=True)   # 3 n-blocks

@@ -145,6 +145,33 @@ def test_small_plain_problems_get_smaller_tiles():
     assert (s["cta_group"], s["block_n"]) == (2, 256)
 
 
+def test_wide_tiles_resolve():
+    """A scheduled tile covers two n-blocks; explicit request only."""
+    cfg = _cfg("plain", 1, 0, 8192, 1024, 8192)
+    assert len(set(_tiles_raw(cfg, 32 * 4))) == 32 * 4             # auto: 256 x 256 tiles
+    cfg.wide_n = 1
+    sched = _schedule(cfg)
+    tiles = _tiles_raw(cfg, sched["num_m_blocks"] * sched["num_n_blocks"] // 2)
+    assert sorted(tiles) == sorted((mb, nb) for mb in range(32) for nb in range(2))
+    cfg = _cfg("ag_before", 2, 0, 8192, 1024, 8192)
+    cfg.wide_n = 1
+    assert len(set(_tiles_raw(cfg, 32 * 2))) == 32 * 2
+    cfg = _cfg("plain", 1, 0, 8192, 768, 8192)                     # 3 n-blocks: not eligible
+    assert len(set(_tiles_raw(cfg, 32 * 3))) == 32 * 3
+    cfg.wide_n = 1
+    with pytest.raises(N.NativeError, match="wide_n"):
+        _schedule(cfg)
+
+
+def _tiles_raw(cfg, count):
+    lib = N.lib()
+    out = (ctypes.c_int32 * (4 * count))()
+    rc = lib.ddlb_debug_tile_coords(ctypes.byref(cfg), 0, count, out)
+    if rc != 0:
+        raise N.NativeError(lib.ddlb_last_error().decode())
+    return [(out[4 * i], out[4 * i + 1]) for i in range(count)]
+
+
 @pytest.mark.parametrize("kwargs,needle", [
     (dict(mode="rs", world=3, rank=0, m=300, n=64, k=192), "multiple of"),          # rows/rank % 128
     (dict(mode="ag_before", world=2, rank=0, m=512, n=100, k=64), "multiple of"),    # n % 64 (and % 8)
