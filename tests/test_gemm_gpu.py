@@ -84,7 +84,7 @@ def test_two_pair_clusters_multicast_a(shape, b_is_nk):
         pytest.skip("B [k,n] needs n % 64 == 0")
     b = b_kn.t().contiguous() if b_is_nk else b_kn
     plan, out = plain_gemm_plan(a, b, b_is_nk=b_is_nk, cta_group=2, block_n=256, cluster_pairs=2)
-    assert plan.info["cluster"] == 2 and plan.info["grid"] % 4 == 0
+    assert plan.info["cluster"] == 4 and plan.info["pairs"] == 2 and plan.info["grid"] % 4 == 0
     for _ in range(2):
         out.fill_(float("nan"))
         plan.run()
