@@ -817,16 +817,19 @@ __device__ __forceinline__ void tp_gemm_body(const TpGemmParams& p, const int cl
       for (int t = cluster; t < num_tiles; t += nclusters) {
         for (int kb = 0; kb < p.num_k_blocks; ++kb) {
           mbar_wait(bar_full + stage * 8, phase);            // this CTA's half has landed
-          uint8_t* base = smem_ops + stage * Cfg::kStageBytes;
+          const uint32_t base = smem_u32(smem_ops + stage * Cfg::kStageBytes);
           constexpr int kVecs = Cfg::kStageOps / 16;         // 16-byte vectors in A + B
           for (int v = sw * 32 + lane; v < kVecs; v += 128) {
-            float4 x = *reinterpret_cast<const float4*>(base + v * 16);
-            float4 lo;
-            lo.x = x.x - __uint_as_float(__float_as_uint(x.x) & 0xffffe000u);
-            lo.y = x.y - __uint_as_float(__float_as_uint(x.y) & 0xffffe000u);
-            lo.z = x.z - __uint_as_float(__float_as_uint(x.z) & 0xffffe000u);
-            lo.w = x.w - __uint_as_float(__float_as_uint(x.w) & 0xffffe000u);
-            *reinterpret_cast<float4*>(base + Cfg::kStageOps + v * 16) = lo;
+            // shared-state-space accesses (a generic float4* compiles to LD.E / ST.E here)
+            uint32_t x0, x1, x2, x3;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(x0), "=r"(x1), "=r"(x2), "=r"(x3) : "r"(base + v * 16) : "memory");
+            const uint32_t l0 = __float_as_uint(__uint_as_float(x0) - __uint_as_float(x0 & 0xffffe000u));
+            const uint32_t l1 = __float_as_uint(__uint_as_float(x1) - __uint_as_float(x1 & 0xffffe000u));
+            const uint32_t l2 = __float_as_uint(__uint_as_float(x2) - __uint_as_float(x2 & 0xffffe000u));
+            const uint32_t l3 = __float_as_uint(__uint_as_float(x3) - __uint_as_float(x3 & 0xffffe000u));
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};"
+                         :: "r"(base + Cfg::kStageOps + v * 16), "r"(l0), "r"(l1), "r"(l2), "r"(l3) : "memory");
           }
           fence_proxy_async_smem();                          // generic writes -> tensor-core reads
           __syncwarp();
