@@ -121,7 +121,7 @@ static int resolve(const ddlb_tp_gemm_config& c, Resolved& r) {
   // of a pair computes 128x128) while one wave still holds all tiles. Measured at 1024^3: 16 tiles
   // on 32 SMs took 13.8 us against cuBLAS' 8.5 us.
   if (c.mode == DDLB_MODE_PLAIN && c.cta_group == 0 && c.block_n == 0 && r.pairs == 1 && r.elem == 2 &&
-      c.n > 128) {
+      c.n > 128 && c.wide_n != 1) {                      // a wide-tile request implies BLOCK_N 256
     const int64_t mb256 = (c.m + 255) / 256, nb128 = (c.n + 127) / 128;
     if (mb256 * nb128 <= r.grid / 2) r.block_n = 128;
   }

@@ -28,6 +28,10 @@ tile-schedule parameters of the kernel:
                    (nvFuser ``offset_stream_indexing_by_rank=False``).
 ``cta_group``      tcgen05 ``cta_group`` (0 = auto: 2 when rows/rank % 256 == 0).
 ``fp32_mode``      float32 only: ``3xtf32`` (default, ~fp32 accuracy) or ``tf32``.
+``tile``           ``default`` (256 x 256 per CTA pair) or ``wide`` (256 x 512: two
+                   accumulators share every A stage; fp16/bf16, cta_group 2, an even number
+                   of 256-column blocks; measured 0.80 - 1.03x on one GPU, multi-rank runs
+                   of it were checked in single-GPU emulation only).
 =================  ==========================================================
 """
 from __future__ import annotations
@@ -45,6 +49,7 @@ class FusedTPColumnwise(TPColumnwise):
         "transport": "auto",
         "rank_rotate": True,
         "fp32_mode": "3xtf32",
+        "tile": "default",
     }
     ALLOWED_VALUES = {
         "order": ["AG_before", "AG_after"],
@@ -55,6 +60,7 @@ class FusedTPColumnwise(TPColumnwise):
         "transport": ["auto", "p2p", "pull", "push", "multimem", "tma", "st128"],
         "rank_rotate": [True, False],
         "fp32_mode": ["3xtf32", "tf32"],
+        "tile": ["default", "wide"],
     }
 
     def __init__(self, *args, **kwargs):
@@ -81,6 +87,7 @@ class FusedTPColumnwise(TPColumnwise):
             cta_group=int(self.options["cta_group"]), block_n=int(self.options["block_n"]),
             transport=self.options["transport"], fp32_mode=self.options["fp32_mode"],
             unrotated=not self.options["rank_rotate"],
+            wide_n=True if self.options["tile"] == "wide" else None,
         ) if d > 1 else self._single_rank_op()
         self.op.a_shard.copy_(self.A)
         self.A = self.op.a_shard
@@ -94,7 +101,8 @@ class FusedTPColumnwise(TPColumnwise):
         return FusedAllGatherGemm(
             None, 0, 1, self.m, self.n, self.k, self.torch_dtype, self.B, order="AG_after",
             cta_group=int(self.options["cta_group"]), block_n=int(self.options["block_n"]),
-            fp32_mode=self.options["fp32_mode"])
+            fp32_mode=self.options["fp32_mode"],
+            wide_n=True if self.options["tile"] == "wide" else None)
 
     def _chunk_rows(self, rows: int) -> int:
         algo = self.options["algorithm"]

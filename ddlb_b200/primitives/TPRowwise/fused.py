@@ -17,6 +17,7 @@ before slab j+1.
 ``transport``: ``push`` (default/``auto``/``p2p``: partials go to the owner's staging, own
 tiles last), ``pull`` (partials stay local, owners load them over NVLink), ``multimem``
 (``multimem.ld_reduce``: the NVSwitch adds the d copies).
+``tile``: ``default`` or ``wide`` (256 x 512 per CTA pair, see the tp_columnwise twin).
 """
 from __future__ import annotations
 
@@ -32,6 +33,7 @@ class FusedTPRowwise(TPRowwise):
         "transport": "auto",
         "rank_rotate": True,
         "fp32_mode": "3xtf32",
+        "tile": "default",
     }
     ALLOWED_VALUES = {
         "algorithm": ["default", "coll_pipeline", "p2p_pipeline"],
@@ -41,6 +43,7 @@ class FusedTPRowwise(TPRowwise):
         "transport": ["auto", "p2p", "push", "pull", "multimem"],
         "rank_rotate": [True, False],
         "fp32_mode": ["3xtf32", "tf32"],
+        "tile": ["default", "wide"],
     }
 
     def __init__(self, *args, **kwargs):
@@ -70,7 +73,8 @@ class FusedTPRowwise(TPRowwise):
             heap, comm.rank, d, self.m, self.n, self.k, self.torch_dtype, self.A, self.B,
             chunk_rows=chunk_rows, cta_group=int(self.options["cta_group"]),
             block_n=int(self.options["block_n"]), transport=self.options["transport"],
-            fp32_mode=self.options["fp32_mode"], unrotated=not self.options["rank_rotate"])
+            fp32_mode=self.options["fp32_mode"], unrotated=not self.options["rank_rotate"],
+            wide_n=True if self.options["tile"] == "wide" else None)
         torch.cuda.synchronize()
         if d > 1:
             heap.barrier()

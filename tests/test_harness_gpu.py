@@ -9,11 +9,11 @@ pytestmark = pytest.mark.gpu
 
 
 @pytest.mark.parametrize("primitive,impls", [
-    ("tp_columnwise", {"fused": [{"order": ["AG_before", "AG_after"]}],
+    ("tp_columnwise", {"fused": [{"order": ["AG_before", "AG_after"], "tile": ["default", "wide"]}],
                        "fuser": [{"algorithm": "coll_pipeline", "s": 2}],
                        "transformer_engine": [{}], "jax": [{}],
                        "pytorch": [{"backend": "nccl"}], "compute_only": [{"size": "unsharded"}]}),
-    ("tp_rowwise", {"fused": [{"algorithm": ["default", "coll_pipeline"]}],
+    ("tp_rowwise", {"fused": [{"algorithm": ["default", "coll_pipeline"]}, {"tile": "wide"}],
                     "fuser": [{"algorithm": "p2p_pipeline"}], "transformer_engine": [{}],
                     "pytorch": [{"backend": "nccl"}], "compute_only": [{}]}),
 ])

@@ -162,6 +162,14 @@ def test_launcher_propagates_failure_and_stops_other_ranks(tmp_path):
     assert __import__("time").time() - t0 < 40          # rank 0 was stopped, not waited for
 
 
+def test_fused_tile_option_is_validated():
+    from ddlb_b200.primitives.TPColumnwise.fused import FusedTPColumnwise
+    from ddlb_b200.primitives.TPRowwise.fused import FusedTPRowwise
+    for cls in (FusedTPColumnwise, FusedTPRowwise):
+        assert cls.DEFAULT_OPTIONS["tile"] == "default"
+        assert cls.ALLOWED_VALUES["tile"] == ["default", "wide"]
+
+
 def test_launcher_sets_rank_environment(tmp_path):
     script = tmp_path / "env.py"
     script.write_text("import os\n"

@@ -153,6 +153,10 @@ def test_wide_tiles_resolve():
     sched = _schedule(cfg)
     tiles = _tiles_raw(cfg, sched["num_m_blocks"] * sched["num_n_blocks"] // 2)
     assert sorted(tiles) == sorted((mb, nb) for mb in range(32) for nb in range(2))
+    cfg = _cfg("plain", 1, 0, 1024, 512, 512)                      # small: auto would pick BLOCK_N 128
+    assert _schedule(cfg)["block_n"] == 128
+    cfg.wide_n = 1                                                 # the request keeps BLOCK_N 256
+    assert _schedule(cfg)["block_n"] == 256 and len(set(_tiles_raw(cfg, 4))) == 4
     cfg = _cfg("ag_before", 2, 0, 8192, 1024, 8192)
     cfg.wide_n = 1
     assert len(set(_tiles_raw(cfg, 32 * 2))) == 32 * 2
