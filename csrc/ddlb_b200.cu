@@ -40,7 +40,7 @@ static int set_error(const char* fmt, ...) {
 }  // namespace ddlb
 
 extern "C" const char* ddlb_last_error(void) { return ddlb::g_last_error; }
-extern "C" int ddlb_version(void) { return 100; }
+extern "C" int ddlb_version(void) { return 200; }   // 0.2.0: config gained pdl, wide_n; info has 12 slots
 
 #include "tp_gemm_sm100.cuh"
 #include "tp_gemm_host.inl"
