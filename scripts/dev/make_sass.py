@@ -42,8 +42,9 @@ def main():
         demangled = subprocess.run(["c++filt", name], capture_output=True, text=True).stdout.strip() or name
         rows.append((demangled, name, len(instr), counts, usage.get(name, ("?", "?"))))
         if any(f in name for f in FLAGSHIP):
-            with gzip.open(os.path.join(OUT, re.sub(r"[^A-Za-z0-9_]", "_", name)[:120] + ".sass.gz"), "wt") as fh:
-                fh.write("// " + demangled + "\n" + "\n".join(lines))
+            path = os.path.join(OUT, re.sub(r"[^A-Za-z0-9_]", "_", name)[:120] + ".sass.gz")
+            with open(path, "wb") as raw, gzip.GzipFile(fileobj=raw, mode="wb", filename="", mtime=0) as fh:
+                fh.write(("// " + demangled + "\n" + "\n".join(lines)).encode())   # mtime 0: reproducible
     show = ["UTCHMMA", "UTMALDG", "UTMASTG", "LDTM", "UTCBAR", "LDGMC", "REDG", "LDG.E.EF.128", "STG.E.128",
             "MEMBAR.ALL.SYS", "CCTL.IVALL", "HMMA"]
     with open(os.path.join(OUT, "INDEX.md"), "w") as fh:
