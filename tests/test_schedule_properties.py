@@ -119,6 +119,36 @@ def test_every_tile_once_and_rows_belong_to_their_part(args):
         assert all(t[2] == rank and t[3] == 0 for t in tiles)
 
 
+@settings(max_examples=150, deadline=None, suppress_health_check=[HealthCheck.too_slow])
+@given(st.sampled_from(["plain", "ag_before", "ag_after", "rs"]), st.sampled_from([1, 2, 4, 8]),
+       st.integers(1, 12), st.integers(1, 6), st.sampled_from([0, 1, 3, 8]), st.booleans(), st.data())
+def test_wide_tiles_cover_every_pair_of_n_blocks_once(mode, world, mult, n_pairs, group_m, unrot, data):
+    """wide_n=1: the scheduled grid is m-blocks x PAIRS of n-blocks; shard / chunk bookkeeping of
+    the multi-rank modes is the one of the ordinary schedule."""
+    if mode == "plain":
+        world = 1
+    rank = data.draw(st.integers(0, world - 1))
+    part_rows = mult * 256
+    m, n, k = part_rows * world, 512 * n_pairs - data.draw(st.sampled_from([0, 64, 192])), 64 * world
+    cfg = _cfg(mode, world, rank, m, n, k, cta_group=2, block_n=256, group_m=group_m, unrotated=unrot)
+    cfg.wide_n = 1
+    sched = _schedule(cfg)
+    nm, nn = sched["num_m_blocks"], sched["num_n_blocks"]
+    assert nn == 2 * n_pairs and sched["block_n"] == 256 and sched["cta_group"] == 2
+    lib = N.lib()
+    total = nm * n_pairs
+    buf = (ctypes.c_int32 * (4 * total))()
+    N.check(lib.ddlb_debug_tile_coords(ctypes.byref(cfg), 0, total, buf), "tile_coords")
+    tiles = [tuple(buf[4 * i:4 * i + 4]) for i in range(total)]
+    assert sorted((t[0], t[1]) for t in tiles) == [(i, j) for i in range(nm) for j in range(n_pairs)]
+    one_more = (ctypes.c_int32 * 4)()
+    assert lib.ddlb_debug_tile_coords(ctypes.byref(cfg), total, 1, one_more) != 0     # nothing beyond
+    if mode in ("ag_before", "rs"):
+        per_part, cm = sched["mblks_per_part"], sched["chunk_mblks"]
+        for m_blk, _, part, chunk in tiles:
+            assert part == m_blk // per_part and chunk == (m_blk % per_part) // cm
+
+
 def test_headline_configs_resolve_as_documented():
     s = _schedule(_cfg("ag_before", 8, 3, 65536, 1024, 1024))
     assert (s["cta_group"], s["block_n"], s["tile_m"]) == (2, 256, 256)
